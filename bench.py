@@ -1,0 +1,393 @@
+#!/usr/bin/env python3
+"""bench.py -- workdir checksum throughput (BASELINE.json metric) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one pass of the hot path over one batch of synthetic input.  The workload is
+BASELINE.json configs[1] ("C2"): a workdir of 1,048,576 files x 4 KiB per GPU, one MD5 per file
+(the manifest rclone's checkers would build one file at a time).  Units are independent, so at
+N GPUs every rank hashes its own shard of N x 1 Mi files with no data-path collective (weak
+scaling); torch.distributed only provides the barrier and the max-over-ranks of the timings.
+
+Numbers on the JSON line:
+  value      kernel-only GB/s (10^9 bytes of file content per second), inputs resident in HBM,
+             timed with CUDA events on the launching stream
+  e2e        the same metric through the host-pointer C-ABI call a cgo caller makes
+             (tpimd5_hash_buffers): pinned host buffer -> H2D -> kernel -> D2H of the digests,
+             all inside the timed region
+  roofline   the lanes kernel against measured HBM copy bandwidth (MEASURED_PEAKS.json), plus
+             the register-only integer-issue ceiling measured in the same run
+  cpu_baseline  OpenSSL MD5 (stand-in for Go crypto/md5; Go is not installed on this image)
+             driven like rclone's per-file hashing on the box's host cores, bounded sample
+`--impl reference` times that CPU path alone, all host threads, and prints the same line shape.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "Workdir checksum GB/s (MD5 + S3 ETag) at 1/2/4/8 B200 vs Go crypto/md5"
+FILE_BYTES = 4096
+FILES_PER_GPU = 1 << 20
+SEED = 2
+WORKLOAD = "C2: 1,048,576 files x 4 KiB per GPU, one-lane-per-file MD5 manifest"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--variant", type=int, default=int(os.environ.get("TPIMD5_VARIANT", "0")))
+    ap.add_argument("--files", type=int, default=FILES_PER_GPU, help="files per GPU (default: the C2 size)")
+    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--sweep", action="store_true", help="print kernel-only GB/s for every kernel variant, then exit")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks during the timed region (NVML; falls back to nvidia-smi)
+# ------------------------------------------------------------------------------------------------
+REASON_BITS = {
+    0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+    0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+    0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting",
+}
+
+
+class ClockSampler:
+    def __init__(self, index: int, period_s: float = 0.05):
+        self.index, self.period = index, period_s
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+        self._nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nvml = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self._nvml = None
+
+    def _sample(self):
+        if self._nvml is not None:
+            p = self._nvml
+            try:
+                self.samples.append(float(p.nvmlDeviceGetClockInfo(self._h, p.NVML_CLOCK_SM)))
+                try:
+                    mask = p.nvmlDeviceGetCurrentClocksEventReasons(self._h)
+                except Exception:
+                    mask = p.nvmlDeviceGetCurrentClocksThrottleReasons(self._h)
+                for bit, name in REASON_BITS.items():
+                    if mask & bit and name != "gpu_idle":
+                        self.reasons.add(name)
+                return
+            except Exception:
+                pass
+        try:
+            import subprocess
+            out = subprocess.check_output(
+                ["nvidia-smi", f"--id={self.index}", "--query-gpu=clocks.sm,clocks.max.sm,clocks_event_reasons.active",
+                 "--format=csv,noheader,nounits"], timeout=5).decode().strip().split(",")
+            self.samples.append(float(out[0]))
+            self.max_mhz = float(out[1])
+            mask = int(out[2].strip(), 16)
+            for bit, name in REASON_BITS.items():
+                if mask & bit and name != "gpu_idle":
+                    self.reasons.add(name)
+        except Exception:
+            pass
+
+    def __enter__(self):
+        def run():
+            while not self._stop.is_set():
+                self._sample()
+                self._stop.wait(self.period)
+        self._thread = threading.Thread(target=run, daemon=True)
+        self._thread.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        self._thread.join()
+
+    def summary(self):
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle's OpenSSL engine, one file per task on all host threads
+# ------------------------------------------------------------------------------------------------
+def cpu_pass(sample, off, ln, threads):
+    import oracle
+    eng = oracle.ENGINE_OPENSSL if oracle.lib().orc_has_openssl() else oracle.ENGINE_RESTATED
+    t0 = time.perf_counter()
+    oracle.md5_batch(sample, off, ln, threads=threads, engine=eng)
+    return time.perf_counter() - t0, eng
+
+
+def cpu_sample_data(n_files):
+    import oracle
+    buf = np.empty(n_files * FILE_BYTES, dtype=np.uint8)
+    oracle.lib()  # build/load
+    for i in range(n_files):
+        oracle.lib().orc_synth_fill(SEED, i, 0, buf[i * FILE_BYTES:].ctypes.data, FILE_BYTES)
+    off = np.arange(n_files, dtype=np.uint64) * FILE_BYTES
+    ln = np.full(n_files, FILE_BYTES, dtype=np.uint64)
+    return buf, off, ln
+
+
+def cpu_baseline(budget_s=12.0, sample_files=1 << 16, host_buf=None):
+    import oracle
+    threads = os.cpu_count() or 1
+    if host_buf is not None:
+        sample = host_buf[: sample_files * FILE_BYTES]
+        off = np.arange(sample_files, dtype=np.uint64) * FILE_BYTES
+        ln = np.full(sample_files, FILE_BYTES, dtype=np.uint64)
+    else:
+        sample, off, ln = cpu_sample_data(sample_files)
+    cpu_pass(sample, off, ln, threads)                      # warm (page in, spin up)
+    passes, spent, eng = 0, 0.0, 0
+    while spent < budget_s and passes < 10000:
+        dt, eng = cpu_pass(sample, off, ln, threads)
+        spent += dt
+        passes += 1
+    gbs = passes * sample.size / spent / 1e9
+    kind = "OpenSSL MD5 (asm), 32 KiB updates" if eng == oracle.ENGINE_OPENSSL else "restated C MD5"
+    return {"value": round(gbs, 3), "unit": "GB/s", "cores": threads, "kind": "port",
+            "sample": f"{sample_files} files x {FILE_BYTES} B of the C2 workdir ({sample.size >> 20} MiB), {passes} passes "
+                      f"in {spent:.1f} s, {kind}, one file per task on {threads} threads; Go crypto/md5 + rclone "
+                      f"not runnable here (no Go toolchain)"}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the CPU implementation of the path, all host threads, rank 0 only."""
+    if rank != 0:
+        return
+    import oracle
+    threads = os.cpu_count() or 1
+    sample_files = 1 << 16
+    sample, off, ln = cpu_sample_data(sample_files)
+    for _ in range(args.warmup):
+        cpu_pass(sample, off, ln, threads)
+    # each step: as many passes over the bounded sample as fit ~1 s, so K steps stay within minutes
+    dt0, eng = cpu_pass(sample, off, ln, threads)
+    reps = max(1, min(64, int(1.0 / max(dt0, 1e-4))))
+    t_total = 0.0
+    for _ in range(args.steps):
+        for _ in range(reps):
+            dt, eng = cpu_pass(sample, off, ln, threads)
+            t_total += dt
+    bytes_step = reps * sample.size
+    gbs = args.steps * bytes_step / t_total / 1e9
+    kind = "OpenSSL MD5 (asm)" if eng == oracle.ENGINE_OPENSSL else "restated C MD5"
+    sample_txt = (f"per step {reps} passes over {sample_files} files x {FILE_BYTES} B of the C2 workdir "
+                  f"({bytes_step >> 20} MiB), {kind}, one file per task on {threads} host threads; stand-in for Go "
+                  f"crypto/md5 + rclone, which cannot run here (no Go toolchain)")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": round(gbs, 3), "unit": "GB/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * t_total / args.steps, 3),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "file_bytes": FILE_BYTES, "files_per_gpu": args.files},
+        "cpu_baseline": {"value": round(gbs, 3), "unit": "GB/s", "cores": threads, "kind": "port", "sample": sample_txt},
+        "e2e": {"value": round(gbs, 3), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    import tpi_b200 as tpi
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the checksum path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    use_dist = world > 1
+    if use_dist:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if use_dist:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if not use_dist:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    n, flen = args.files, FILE_BYTES
+    nbytes = n * flen
+    ctx = tpi.Context([local_rank])
+    if args.variant:
+        ctx.set_variant(args.variant)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    data = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    digests = torch.empty((n, 16), dtype=torch.uint8, device=dev)
+    ctx.dev_synth_fill(data, SEED, rank * n, flen, n, stream=stream)       # this rank's shard of the workdir
+    torch.cuda.synchronize()
+
+    def step():
+        ctx.dev_hash_buffers(data, nbytes, n, digests, stride=flen, stream=stream)
+
+    if args.sweep:
+        for variant in [1, 2, 3, 4, 5, 6, 11, 12, 14, 21, 22, 24, 31, 32, 34]:
+            ctx.set_variant(variant)
+            for _ in range(3):
+                step()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(10):
+                step()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / 10
+            print(json.dumps({"variant": variant, "ms": round(ms, 4), "GBps": round(nbytes / ms / 1e6, 1)}), flush=True)
+        probe_out = torch.empty(148 * 16 * 128 * 16, dtype=torch.uint8, device=dev)
+        for mode in range(4):
+            for ctas in (2, 4, 8):
+                ctx.dev_int_probe(mode, ctas, 64, probe_out, stream=stream)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                blocks = ctx.dev_int_probe(mode, ctas, 4096, probe_out, stream=stream)
+                e1.record()
+                torch.cuda.synchronize()
+                ms = e0.elapsed_time(e1)
+                print(json.dumps({"probe_mode": mode, "warps_per_sm": ctas * 4, "ms": round(ms, 3),
+                                  "GBps_equiv": round(blocks * 64 / ms / 1e6, 1)}), flush=True)
+        return 0
+
+    # ---- kernel-only: W warm-up + K timed steps; 4 GiB of input per step >> 126 MB of L2 ---------
+    args.warmup = max(args.warmup, 3)          # timing rule: at least 3 warm-up steps
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    launches0 = ctx.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clocks:
+        e0.record()
+        for _ in range(args.steps):
+            step()
+        e1.record()
+        barrier()
+    launches = ctx.launch_count() - launches0
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    ms_step = ms_total / args.steps
+    value = world * nbytes / (ms_step * 1e-3) / 1e9
+    kernel_ms_local = e0.elapsed_time(e1) / args.steps            # one lanes-kernel launch per step
+
+    # ---- integer-issue ceiling: the same 64-step body, registers only ----------------------------
+    mode = (args.variant // 10) if args.variant else 0
+    probe_out = torch.empty(148 * 16 * 128 * 16, dtype=torch.uint8, device=dev)
+    ctx.dev_int_probe(mode, 4, 64, probe_out, stream=stream)
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    p0.record()
+    probe_blocks = ctx.dev_int_probe(mode, 4, 2048, probe_out, stream=stream)
+    p1.record()
+    torch.cuda.synchronize()
+    int_peak = probe_blocks * 64 / (p0.elapsed_time(p1) * 1e-3) / 1e9
+
+    # ---- end to end through the host-pointer entry point -----------------------------------------
+    e2e = None
+    host_np = None
+    if not args.no_e2e:
+        host = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+        host.copy_(data)
+        torch.cuda.synchronize()
+        host_np = host.numpy()
+        off = np.arange(n, dtype=np.uint64) * flen
+        ln = np.full(n, flen, dtype=np.uint64)
+        out = None
+        for _ in range(2):
+            out = ctx.hash_buffers(host_np, off, ln)
+        if not np.array_equal(out, digests.cpu().numpy()):
+            raise SystemExit("bench.py: end-to-end digests differ from the kernel-only digests")
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.e2e_steps):
+            out = ctx.hash_buffers(host_np, off, ln)
+        barrier()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        e2e = {"value": round(world * nbytes * args.e2e_steps / dt / 1e9, 3), "unit": "GB/s",
+               "h2d_bytes_per_step": int(nbytes + n * 32), "d2h_bytes_per_step": int(n * 16),
+               "steps": args.e2e_steps, "ms_per_step": round(1e3 * dt / args.e2e_steps, 3),
+               "api": "tpimd5_hash_buffers (host pointers, pinned source, H2D + kernel + D2H inside the timed region)"}
+
+    # ---- CPU baseline beside it (rank 0, N=1 only) ------------------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu = cpu_baseline(host_buf=host_np)
+
+    if rank == 0:
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(peaks_path):
+            peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+        else:
+            peak, peak_src = 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
+        achieved = nbytes / (kernel_ms_local * 1e-3) / 1e9
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath):
+            try:
+                traffic = json.load(open(tpath)).get("md5_lanes_kernel_bytes_per_launch")
+            except Exception:
+                traffic = None
+        line = {
+            "metric": METRIC, "value": round(value, 3), "unit": "GB/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "file_bytes": flen, "files_per_gpu": n, "bytes_per_gpu_per_step": nbytes,
+                       "l2": "4 GiB of input per step, far larger than the 126 MB L2 (no flush needed)",
+                       "kernel_variant": args.variant, "sharding": "independent shard per rank, no collective"},
+            "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                         "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
+                         "kernel": "md5_lanes_kernel", "algorithmic_bytes_per_launch": nbytes,
+                         "int_issue_peak_GBps": round(int_peak, 1), "frac_of_int_issue": round(achieved / int_peak, 4),
+                         "int_issue_source": "register-only probe of the same 64-step body, 16 warps/SM, same run"},
+            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks.summary(),
+        }
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if use_dist:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

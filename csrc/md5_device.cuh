@@ -1,0 +1,172 @@
+// md5_device.cuh -- the MD5 compression function as sm_100a integer code.
+//
+// One thread owns one MD5 chain (one "lane": a file, an S3 part or a stream).  The arithmetic is
+// RFC 1321 section 3.4, which is what Go's crypto/md5 block function computes for
+// [rclone] fs/hash StreamTypes (reached from /root/reference/task/common/machine/storage.go:158).
+// Message words are little-endian, so bytes staged in shared memory are used as they are.
+//
+// Instruction budget per step: one LOP3 (F/G/H/I are single 3-input LUT ops), one SHF.L.W rotate
+// and three additions.  `m + k` does not depend on the chain and `a + (m + k)` only on a value
+// that was final three steps earlier, so the dependent chain per step is LOP3 -> add -> SHF -> add.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace tpimd5 {
+
+__device__ __forceinline__ uint32_t rotl(uint32_t x, int s) { return __funnelshift_l(x, x, s); }
+
+// lop3 with an explicit truth table keeps ptxas from splitting the boolean into two ops.
+template <int LUT>
+__device__ __forceinline__ uint32_t lop3(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %3, %4;" : "=r"(r) : "r"(a), "r"(b), "r"(c), "n"(LUT));
+    return r;
+}
+// truth tables for inputs (b, c, d) = (0xF0, 0xCC, 0xAA)
+__device__ __forceinline__ uint32_t fF(uint32_t b, uint32_t c, uint32_t d) { return lop3<0xCA>(b, c, d); }  // (b&c)|(~b&d)
+__device__ __forceinline__ uint32_t fG(uint32_t b, uint32_t c, uint32_t d) { return lop3<0xE4>(b, c, d); }  // (b&d)|(c&~d)
+__device__ __forceinline__ uint32_t fH(uint32_t b, uint32_t c, uint32_t d) { return lop3<0x96>(b, c, d); }  // b^c^d
+__device__ __forceinline__ uint32_t fI(uint32_t b, uint32_t c, uint32_t d) { return lop3<0x39>(b, c, d); }  // c^(b|~d)
+
+// How the three additions of a step are issued.  sm_100a has two integer-capable pipes per SM
+// sub-partition (alu: LOP3/IADD3/SHF/LEA, fma: IMAD), each taking one warp instruction every other
+// cycle.  LOP3 and the fused rotate-add (LEA.HI) must go to alu; the additions can go either way,
+// but only if the compiler is stopped from folding them back into IADD3: `mad.lo` by a register
+// that holds 1 (`one`, a kernel argument the compiler cannot see through) is an add on the fma pipe.
+//   MODE 0  plain C, ptxas decides (it emits LOP3, IADD3, VIADD, LEA.HI: four alu ops, 8 cycles/step)
+//   MODE 1  m+k on fma, a+x+f as one IADD3 on alu          -> alu 3, fma 1
+//   MODE 3  m+k, a+x and y+f all on fma                    -> alu 2, fma 3
+//   MODE 2  steps alternate between 1 and 3                -> alu 2.5, fma 2 on average
+__device__ __forceinline__ uint32_t mad1(uint32_t a, uint32_t one, uint32_t c) {
+    uint32_t r;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(one), "r"(c));
+    return r;
+}
+
+template <int MODE, int STEP_PARITY>
+__device__ __forceinline__ uint32_t step_sum(uint32_t a, uint32_t f, uint32_t m, uint32_t k, uint32_t one) {
+    if (MODE == 0) {
+        return (a + (m + k)) + f;
+    } else if (MODE == 1 || (MODE == 2 && STEP_PARITY == 0)) {
+        const uint32_t x = mad1(m, one, k);
+        return a + x + f;
+    } else {
+        const uint32_t x = mad1(m, one, k);
+        const uint32_t y = mad1(a, one, x);
+        return mad1(f, one, y);
+    }
+}
+
+#define TPI_STEP(f, a, b, c, d, m, k, s)                                         \
+    {                                                                            \
+        const uint32_t t_ = step_sum<MODE, (s) & 1>((a), f((b), (c), (d)), (m), (uint32_t)(k), one); \
+        (a) = (b) + rotl(t_, (s));                                               \
+    }
+
+// One 64-byte block: st <- compress(st, m[0..15]).
+template <int MODE>
+__device__ __forceinline__ void md5_block(uint32_t (&st)[4], const uint32_t (&m)[16], uint32_t one) {
+    uint32_t a = st[0], b = st[1], c = st[2], d = st[3];
+    // round 1: g = i
+    TPI_STEP(fF, a, b, c, d, m[0], 0xd76aa478u, 7)
+    TPI_STEP(fF, d, a, b, c, m[1], 0xe8c7b756u, 12)
+    TPI_STEP(fF, c, d, a, b, m[2], 0x242070dbu, 17)
+    TPI_STEP(fF, b, c, d, a, m[3], 0xc1bdceeeu, 22)
+    TPI_STEP(fF, a, b, c, d, m[4], 0xf57c0fafu, 7)
+    TPI_STEP(fF, d, a, b, c, m[5], 0x4787c62au, 12)
+    TPI_STEP(fF, c, d, a, b, m[6], 0xa8304613u, 17)
+    TPI_STEP(fF, b, c, d, a, m[7], 0xfd469501u, 22)
+    TPI_STEP(fF, a, b, c, d, m[8], 0x698098d8u, 7)
+    TPI_STEP(fF, d, a, b, c, m[9], 0x8b44f7afu, 12)
+    TPI_STEP(fF, c, d, a, b, m[10], 0xffff5bb1u, 17)
+    TPI_STEP(fF, b, c, d, a, m[11], 0x895cd7beu, 22)
+    TPI_STEP(fF, a, b, c, d, m[12], 0x6b901122u, 7)
+    TPI_STEP(fF, d, a, b, c, m[13], 0xfd987193u, 12)
+    TPI_STEP(fF, c, d, a, b, m[14], 0xa679438eu, 17)
+    TPI_STEP(fF, b, c, d, a, m[15], 0x49b40821u, 22)
+    // round 2: g = (5i + 1) mod 16
+    TPI_STEP(fG, a, b, c, d, m[1], 0xf61e2562u, 5)
+    TPI_STEP(fG, d, a, b, c, m[6], 0xc040b340u, 9)
+    TPI_STEP(fG, c, d, a, b, m[11], 0x265e5a51u, 14)
+    TPI_STEP(fG, b, c, d, a, m[0], 0xe9b6c7aau, 20)
+    TPI_STEP(fG, a, b, c, d, m[5], 0xd62f105du, 5)
+    TPI_STEP(fG, d, a, b, c, m[10], 0x02441453u, 9)
+    TPI_STEP(fG, c, d, a, b, m[15], 0xd8a1e681u, 14)
+    TPI_STEP(fG, b, c, d, a, m[4], 0xe7d3fbc8u, 20)
+    TPI_STEP(fG, a, b, c, d, m[9], 0x21e1cde6u, 5)
+    TPI_STEP(fG, d, a, b, c, m[14], 0xc33707d6u, 9)
+    TPI_STEP(fG, c, d, a, b, m[3], 0xf4d50d87u, 14)
+    TPI_STEP(fG, b, c, d, a, m[8], 0x455a14edu, 20)
+    TPI_STEP(fG, a, b, c, d, m[13], 0xa9e3e905u, 5)
+    TPI_STEP(fG, d, a, b, c, m[2], 0xfcefa3f8u, 9)
+    TPI_STEP(fG, c, d, a, b, m[7], 0x676f02d9u, 14)
+    TPI_STEP(fG, b, c, d, a, m[12], 0x8d2a4c8au, 20)
+    // round 3: g = (3i + 5) mod 16
+    TPI_STEP(fH, a, b, c, d, m[5], 0xfffa3942u, 4)
+    TPI_STEP(fH, d, a, b, c, m[8], 0x8771f681u, 11)
+    TPI_STEP(fH, c, d, a, b, m[11], 0x6d9d6122u, 16)
+    TPI_STEP(fH, b, c, d, a, m[14], 0xfde5380cu, 23)
+    TPI_STEP(fH, a, b, c, d, m[1], 0xa4beea44u, 4)
+    TPI_STEP(fH, d, a, b, c, m[4], 0x4bdecfa9u, 11)
+    TPI_STEP(fH, c, d, a, b, m[7], 0xf6bb4b60u, 16)
+    TPI_STEP(fH, b, c, d, a, m[10], 0xbebfbc70u, 23)
+    TPI_STEP(fH, a, b, c, d, m[13], 0x289b7ec6u, 4)
+    TPI_STEP(fH, d, a, b, c, m[0], 0xeaa127fau, 11)
+    TPI_STEP(fH, c, d, a, b, m[3], 0xd4ef3085u, 16)
+    TPI_STEP(fH, b, c, d, a, m[6], 0x04881d05u, 23)
+    TPI_STEP(fH, a, b, c, d, m[9], 0xd9d4d039u, 4)
+    TPI_STEP(fH, d, a, b, c, m[12], 0xe6db99e5u, 11)
+    TPI_STEP(fH, c, d, a, b, m[15], 0x1fa27cf8u, 16)
+    TPI_STEP(fH, b, c, d, a, m[2], 0xc4ac5665u, 23)
+    // round 4: g = 7i mod 16
+    TPI_STEP(fI, a, b, c, d, m[0], 0xf4292244u, 6)
+    TPI_STEP(fI, d, a, b, c, m[7], 0x432aff97u, 10)
+    TPI_STEP(fI, c, d, a, b, m[14], 0xab9423a7u, 15)
+    TPI_STEP(fI, b, c, d, a, m[5], 0xfc93a039u, 21)
+    TPI_STEP(fI, a, b, c, d, m[12], 0x655b59c3u, 6)
+    TPI_STEP(fI, d, a, b, c, m[3], 0x8f0ccc92u, 10)
+    TPI_STEP(fI, c, d, a, b, m[10], 0xffeff47du, 15)
+    TPI_STEP(fI, b, c, d, a, m[1], 0x85845dd1u, 21)
+    TPI_STEP(fI, a, b, c, d, m[8], 0x6fa87e4fu, 6)
+    TPI_STEP(fI, d, a, b, c, m[15], 0xfe2ce6e0u, 10)
+    TPI_STEP(fI, c, d, a, b, m[6], 0xa3014314u, 15)
+    TPI_STEP(fI, b, c, d, a, m[13], 0x4e0811a1u, 21)
+    TPI_STEP(fI, a, b, c, d, m[4], 0xf7537e82u, 6)
+    TPI_STEP(fI, d, a, b, c, m[11], 0xbd3af235u, 10)
+    TPI_STEP(fI, c, d, a, b, m[2], 0x2ad7d2bbu, 15)
+    TPI_STEP(fI, b, c, d, a, m[9], 0xeb86d391u, 21)
+    st[0] += a; st[1] += b; st[2] += c; st[3] += d;
+}
+
+// Turns the words of a block that holds only `rem` (0..63) message bytes into the padded block:
+// 0x80 after the data, zeros, and -- when the 8 length bytes still fit (rem <= 55) -- the
+// message length in bits as a 64-bit little-endian count in words 14/15.  A block that comes
+// after the 0x80 block (`after_marker`) is all zeros plus the length.
+__device__ __forceinline__ void md5_pad_block(uint32_t (&m)[16], uint32_t rem, bool after_marker, uint64_t total_bytes) {
+#pragma unroll
+    for (int w = 0; w < 16; ++w) {
+        const uint32_t lo = 4u * w;
+        uint32_t v = m[w];
+        if (after_marker) {
+            v = 0;
+        } else if (rem <= lo) {
+            v = (rem == lo) ? 0x80u : 0u;
+        } else if (rem < lo + 4) {
+            const uint32_t k = 8u * (rem - lo);                 // 8, 16 or 24 valid bits
+            v = (v & ((1u << k) - 1u)) | (0x80u << k);
+        }
+        m[w] = v;
+    }
+    if (after_marker || rem <= 55) {
+        const uint64_t bits = total_bytes << 3;
+        m[14] = (uint32_t)bits;
+        m[15] = (uint32_t)(bits >> 32);
+    }
+}
+
+__device__ __forceinline__ void md5_iv(uint32_t (&st)[4]) {
+    st[0] = 0x67452301u; st[1] = 0xefcdab89u; st[2] = 0x98badcfeu; st[3] = 0x10325476u;
+}
+
+}  // namespace tpimd5

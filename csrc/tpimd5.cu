@@ -1,0 +1,1071 @@
+// tpimd5.cu -- C-ABI (include/tpimd5.h) and host runtime of the B200 checksum path.
+//
+// Layering (bottom up):
+//   md5_device.cuh / md5_lanes.cuh / aux_kernels.cuh   sm_100a kernels
+//   launch_lanes(), tpimd5_dev_*                       kernel launches on device-resident data
+//   Pipeline                                           host ingest: units -> staging -> H2D -> kernel
+//   tpimd5_hash_* / s3 / stream / diff                 the entry points a cgo package binds
+//
+// The host side mirrors what [rclone] does around crypto/md5 for TPI's machine.Transfer
+// (/root/reference/task/common/machine/storage.go:123-159): many independent objects, each
+// read once, one digest each.  There is no CPU hashing anywhere in this file.
+#include "../include/tpimd5.h"
+
+#include <algorithm>
+#include <atomic>
+#include <cerrno>
+#include <condition_variable>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <fcntl.h>
+#include <functional>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <sys/stat.h>
+#include <thread>
+#include <unistd.h>
+#include <vector>
+
+#include "aux_kernels.cuh"
+#include "md5_lanes.cuh"
+
+using namespace tpimd5;
+
+// ------------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------------
+static thread_local std::string g_err;
+
+static int fail(int code, const char *fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CU(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess) return fail(TPIMD5_ECUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                                           __FILE__, __LINE__);                                          \
+    } while (0)
+
+extern "C" const char *tpimd5_last_error(void) { return g_err.c_str(); }
+extern "C" const char *tpimd5_version(void) { return "tpimd5 0.1 (sm_100a)"; }
+
+// ------------------------------------------------------------------------------------------------
+// a small worker pool: packs units into pinned staging / reads files, in parallel
+// ------------------------------------------------------------------------------------------------
+class Pool {
+  public:
+    explicit Pool(int n) {
+        for (int i = 0; i < n; ++i) th_.emplace_back([this] { run(); });
+    }
+    ~Pool() {
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            stop_ = true;
+        }
+        cv_.notify_all();
+        for (auto &t : th_) t.join();
+    }
+    int size() const { return (int)th_.size(); }
+    // fn(i) for i in [0, n), dynamically chunked; returns when all are done.  Callers may overlap.
+    void parallel_for(size_t n, size_t grain, const std::function<void(size_t)> &fn) {
+        if (n == 0) return;
+        if (th_.empty() || n <= grain) {
+            for (size_t i = 0; i < n; ++i) fn(i);
+            return;
+        }
+        auto job = std::make_shared<Job>();
+        job->n = n; job->grain = grain; job->fn = &fn;
+        size_t helpers = std::min<size_t>(th_.size(), (n + grain - 1) / grain);
+        job->pending = helpers + 1;
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            for (size_t i = 0; i < helpers; ++i) q_.push_back(job);
+        }
+        cv_.notify_all();
+        work(*job);                      // the caller helps too
+        std::unique_lock<std::mutex> lk(job->mu);
+        job->cv.wait(lk, [&] { return job->pending == 0; });
+    }
+
+  private:
+    struct Job {
+        size_t n = 0, grain = 1;
+        std::atomic<size_t> next{0};
+        const std::function<void(size_t)> *fn = nullptr;
+        std::mutex mu;
+        std::condition_variable cv;
+        size_t pending = 0;
+    };
+    static void work(Job &j) {
+        for (;;) {
+            size_t lo = j.next.fetch_add(j.grain);
+            if (lo >= j.n) break;
+            size_t hi = std::min(j.n, lo + j.grain);
+            for (size_t i = lo; i < hi; ++i) (*j.fn)(i);
+        }
+        std::lock_guard<std::mutex> g(j.mu);
+        if (--j.pending == 0) j.cv.notify_all();
+    }
+    void run() {
+        for (;;) {
+            std::shared_ptr<Job> job;
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                cv_.wait(lk, [&] { return stop_ || !q_.empty(); });
+                if (stop_ && q_.empty()) return;
+                job = q_.back();
+                q_.pop_back();
+            }
+            work(*job);
+        }
+    }
+    std::vector<std::thread> th_;
+    std::vector<std::shared_ptr<Job>> q_;
+    std::mutex mu_;
+    std::condition_variable cv_;
+    bool stop_ = false;
+};
+
+// ------------------------------------------------------------------------------------------------
+// context
+// ------------------------------------------------------------------------------------------------
+constexpr int NBUF = 3;                       // staging buffers in flight per device
+constexpr size_t MAX_BATCH_LANES = 1u << 20;  // descriptor rows per staging buffer
+constexpr size_t DEFAULT_STAGING = 256u << 20;
+constexpr uint64_t MAX_LANE_BYTES = (uint64_t)60 << 30;  // one unit's bytes per launch (32-bit granule count)
+
+struct LaneDesc {  // device / pinned mirrors, structure of arrays
+    uint64_t *off = nullptr, *len = nullptr, *prior = nullptr;
+    uint32_t *flags = nullptr, *oidx = nullptr;
+};
+
+struct Slot {
+    int dev = -1;
+    std::mutex mu;  // one call at a time per device
+    cudaStream_t s_copy = nullptr, s_comp = nullptr;
+    // ingest staging (allocated on first use)
+    size_t stage_bytes = 0;
+    bool staged = false;
+    uint8_t *h_stage[NBUF] = {}, *d_stage[NBUF] = {};
+    uint8_t *h_desc_raw[NBUF] = {}, *d_desc_raw[NBUF] = {};
+    LaneDesc hd[NBUF], dd[NBUF];
+    cudaEvent_t ev_copied[NBUF] = {}, ev_done[NBUF] = {};
+    // digest / chaining-value table
+    uint4 *d_table = nullptr;
+    uint8_t *h_table = nullptr;
+    size_t table_cap = 0;
+    // scratch: S3 part digests, diff tile counts
+    uint8_t *d_scratch = nullptr;
+    size_t scratch_cap = 0;
+};
+
+struct tpimd5_ctx {
+    std::vector<std::unique_ptr<Slot>> slots;
+    std::unique_ptr<Pool> pool;
+    size_t staging = DEFAULT_STAGING;
+    std::atomic<uint64_t> launches{0};
+    std::atomic<int> variant{0};
+};
+
+static constexpr size_t desc_bytes_per_lane = 3 * sizeof(uint64_t) + 2 * sizeof(uint32_t);
+
+static void carve_desc(uint8_t *raw, size_t cap, LaneDesc &d) {
+    d.off = (uint64_t *)raw;
+    d.len = d.off + cap;
+    d.prior = d.len + cap;
+    d.flags = (uint32_t *)(d.prior + cap);
+    d.oidx = d.flags + cap;
+}
+
+static int ensure_table(Slot &s, size_t rows) {
+    if (rows <= s.table_cap) return 0;
+    size_t cap = std::max<size_t>(rows, 4096);
+    cap = (cap + 4095) & ~(size_t)4095;
+    if (s.d_table) cudaFree(s.d_table);
+    if (s.h_table) cudaFreeHost(s.h_table);
+    s.d_table = nullptr; s.h_table = nullptr; s.table_cap = 0;
+    CU(cudaMalloc(&s.d_table, cap * 16));
+    CU(cudaHostAlloc(&s.h_table, cap * 16, cudaHostAllocDefault));
+    s.table_cap = cap;
+    return 0;
+}
+
+static int ensure_scratch(Slot &s, size_t bytes) {
+    if (bytes <= s.scratch_cap) return 0;
+    size_t cap = (std::max<size_t>(bytes, 1u << 20) + 255) & ~(size_t)255;
+    if (s.d_scratch) cudaFree(s.d_scratch);
+    s.d_scratch = nullptr; s.scratch_cap = 0;
+    CU(cudaMalloc(&s.d_scratch, cap));
+    s.scratch_cap = cap;
+    return 0;
+}
+
+static int ensure_staging(tpimd5_ctx *ctx, Slot &s) {
+    if (s.staged) return 0;
+    s.stage_bytes = ctx->staging;
+    for (int i = 0; i < NBUF; ++i) {
+        CU(cudaHostAlloc(&s.h_stage[i], s.stage_bytes + 256, cudaHostAllocDefault));
+        CU(cudaMalloc(&s.d_stage[i], s.stage_bytes + 256));
+        CU(cudaHostAlloc(&s.h_desc_raw[i], MAX_BATCH_LANES * desc_bytes_per_lane, cudaHostAllocDefault));
+        CU(cudaMalloc(&s.d_desc_raw[i], MAX_BATCH_LANES * desc_bytes_per_lane));
+        carve_desc(s.h_desc_raw[i], MAX_BATCH_LANES, s.hd[i]);
+        carve_desc(s.d_desc_raw[i], MAX_BATCH_LANES, s.dd[i]);
+        CU(cudaEventCreateWithFlags(&s.ev_copied[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&s.ev_done[i], cudaEventDisableTiming));
+    }
+    s.staged = true;
+    return 0;
+}
+
+extern "C" int tpimd5_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+extern "C" int tpimd5_init(const int *device_ids, int n_devices, size_t staging_bytes_per_device, tpimd5_ctx **out) {
+    if (!out || n_devices < 1) return fail(TPIMD5_EINVAL, "tpimd5_init: need out and n_devices >= 1");
+    *out = nullptr;
+    int have = 0;
+    cudaError_t e = cudaGetDeviceCount(&have);
+    if (e != cudaSuccess || have < 1)
+        return fail(TPIMD5_ENODEV, "tpimd5_init: no CUDA device (%s); this library has no CPU fallback",
+                    e == cudaSuccess ? "count is 0" : cudaGetErrorString(e));
+    std::unique_ptr<tpimd5_ctx> ctx(new tpimd5_ctx);
+    if (staging_bytes_per_device) {
+        if (staging_bytes_per_device < (1u << 20)) return fail(TPIMD5_EINVAL, "tpimd5_init: staging below 1 MiB");
+        ctx->staging = (staging_bytes_per_device + 255) & ~(size_t)255;
+    }
+    for (int i = 0; i < n_devices; ++i) {
+        int dev = device_ids ? device_ids[i] : i;
+        if (dev < 0 || dev >= have) return fail(TPIMD5_ENODEV, "tpimd5_init: device %d not present (%d visible)", dev, have);
+        cudaDeviceProp prop;
+        CU(cudaGetDeviceProperties(&prop, dev));
+        if (prop.major != 10)
+            return fail(TPIMD5_ENODEV, "tpimd5_init: device %d is sm_%d%d; this build carries sm_100a code only", dev,
+                        prop.major, prop.minor);
+        std::unique_ptr<Slot> s(new Slot);
+        s->dev = dev;
+        CU(cudaSetDevice(dev));
+        CU(cudaStreamCreateWithFlags(&s->s_copy, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&s->s_comp, cudaStreamNonBlocking));
+        ctx->slots.push_back(std::move(s));
+    }
+    unsigned hc = std::thread::hardware_concurrency();
+    int workers = (int)std::min<unsigned>(hc ? hc : 4, 32);
+    ctx->pool.reset(new Pool(workers > 1 ? workers - 1 : 0));
+    *out = ctx.release();
+    return 0;
+}
+
+extern "C" void tpimd5_destroy(tpimd5_ctx *ctx) {
+    if (!ctx) return;
+    for (auto &sp : ctx->slots) {
+        Slot &s = *sp;
+        cudaSetDevice(s.dev);
+        if (s.s_comp) cudaStreamSynchronize(s.s_comp);
+        if (s.s_copy) cudaStreamSynchronize(s.s_copy);
+        for (int i = 0; i < NBUF; ++i) {
+            if (s.h_stage[i]) cudaFreeHost(s.h_stage[i]);
+            if (s.d_stage[i]) cudaFree(s.d_stage[i]);
+            if (s.h_desc_raw[i]) cudaFreeHost(s.h_desc_raw[i]);
+            if (s.d_desc_raw[i]) cudaFree(s.d_desc_raw[i]);
+            if (s.ev_copied[i]) cudaEventDestroy(s.ev_copied[i]);
+            if (s.ev_done[i]) cudaEventDestroy(s.ev_done[i]);
+        }
+        if (s.d_table) cudaFree(s.d_table);
+        if (s.h_table) cudaFreeHost(s.h_table);
+        if (s.d_scratch) cudaFree(s.d_scratch);
+        if (s.s_copy) cudaStreamDestroy(s.s_copy);
+        if (s.s_comp) cudaStreamDestroy(s.s_comp);
+    }
+    delete ctx;
+}
+
+extern "C" int tpimd5_ctx_devices(const tpimd5_ctx *ctx) { return ctx ? (int)ctx->slots.size() : 0; }
+extern "C" uint64_t tpimd5_launch_count(const tpimd5_ctx *ctx) { return ctx ? ctx->launches.load() : 0; }
+extern "C" int tpimd5_set_variant(tpimd5_ctx *ctx, int variant) {
+    if (!ctx || variant < 0 || variant > 39 || variant % 10 > 6) return fail(TPIMD5_EINVAL, "tpimd5_set_variant: 10*mode(0..3) + shape(0..6)");
+    ctx->variant = variant;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// kernel launch
+// ------------------------------------------------------------------------------------------------
+template <int CH, bool ALIGNED, int WARPS, int MINB, int MODE>
+static int launch_cfg(const LaneArgs &a, cudaStream_t st) {
+    using Cfg = LaneCfg<CH, ALIGNED, WARPS>;
+    auto kern = md5_lanes_kernel<CH, ALIGNED, WARPS, MINB, MODE>;
+    static thread_local int configured_dev = -1;  // per template instantiation and thread
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    if (configured_dev != dev) {
+        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+        CU(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        configured_dev = dev;
+    }
+    const uint64_t per_cta = WARPS * 32;
+    const uint64_t grid = (a.n + per_cta - 1) / per_cta;
+    if (grid == 0) return 0;
+    if (grid > 0x7fffffffull) return fail(TPIMD5_ERANGE, "too many units for one launch (%llu)", (unsigned long long)a.n);
+    kern<<<(unsigned)grid, WARPS * 32, Cfg::SMEM_BYTES, st>>>(a);
+    CU(cudaGetLastError());
+    return 0;
+}
+
+template <bool ALIGNED, int MODE>
+static int launch_variant(int variant, const LaneArgs &a, cudaStream_t st) {
+    switch (variant) {
+        default:
+        case 1: return launch_cfg<128, ALIGNED, 4, 4, MODE>(a, st);   // 16 warps/SM, 144 KiB smem/SM
+        case 2: return launch_cfg<256, ALIGNED, 4, 3, MODE>(a, st);   // 12 warps/SM, 204 KiB
+        case 3: return launch_cfg<64, ALIGNED, 4, 5, MODE>(a, st);    // 20 warps/SM, 100 KiB
+        case 4: return launch_cfg<128, ALIGNED, 4, 5, MODE>(a, st);   // 20 warps/SM, 180 KiB
+        case 5: return launch_cfg<128, ALIGNED, 4, 3, MODE>(a, st);   // 12 warps/SM
+        case 6: return launch_cfg<256, ALIGNED, 2, 6, MODE>(a, st);   // 12 warps/SM in CTAs of 2 warps
+    }
+}
+
+// variant = 10*mode + shape; `aligned`: every unit starts on a 16-byte boundary of device memory.
+static int launch_lanes(tpimd5_ctx *ctx, const LaneArgs &a0, bool aligned, cudaStream_t st) {
+    if (a0.n == 0) return 0;
+    LaneArgs a = a0;
+    a.one = 1u;
+    const int v = ctx->variant.load();
+    const int shape = v % 10, mode = v / 10;
+    int rc;
+    if (aligned) {
+        switch (mode) {
+            default: rc = launch_variant<true, 0>(shape, a, st); break;
+            case 1: rc = launch_variant<true, 1>(shape, a, st); break;
+            case 2: rc = launch_variant<true, 2>(shape, a, st); break;
+            case 3: rc = launch_variant<true, 3>(shape, a, st); break;
+        }
+    } else {
+        switch (mode) {
+            default: rc = launch_variant<false, 0>(shape, a, st); break;
+            case 1: rc = launch_variant<false, 1>(shape, a, st); break;
+            case 2: rc = launch_variant<false, 2>(shape, a, st); break;
+            case 3: rc = launch_variant<false, 3>(shape, a, st); break;
+        }
+    }
+    if (rc == 0) ctx->launches.fetch_add(1);
+    return rc;
+}
+
+static Slot *get_slot(tpimd5_ctx *ctx, int slot) {
+    if (!ctx || slot < 0 || slot >= (int)ctx->slots.size()) return nullptr;
+    return ctx->slots[slot].get();
+}
+
+// ------------------------------------------------------------------------------------------------
+// device-resident entry points
+// ------------------------------------------------------------------------------------------------
+extern "C" int tpimd5_dev_hash_buffers(tpimd5_ctx *ctx, int slot, const void *d_base, uint64_t base_bytes,
+                                       const uint64_t *d_offsets, const uint64_t *d_lengths, uint64_t stride, size_t n,
+                                       void *d_digests_out, void *cuda_stream) {
+    Slot *s = get_slot(ctx, slot);
+    if (!s) return fail(TPIMD5_EINVAL, "dev_hash_buffers: bad context or slot");
+    if (n == 0) return 0;
+    if (!d_base || !d_digests_out) return fail(TPIMD5_EINVAL, "dev_hash_buffers: null pointer");
+    if (((uintptr_t)d_digests_out & 15) != 0) return fail(TPIMD5_EINVAL, "dev_hash_buffers: digests_out must be 16-byte aligned");
+    bool aligned;
+    if (d_offsets) {
+        if (!d_lengths) return fail(TPIMD5_EINVAL, "dev_hash_buffers: offsets without lengths");
+        aligned = false;  // offsets live on the device; the general kernel takes any alignment
+    } else {
+        if (stride == 0) return fail(TPIMD5_EINVAL, "dev_hash_buffers: stride 0");
+        if (stride > MAX_LANE_BYTES) return fail(TPIMD5_ERANGE, "dev_hash_buffers: unit above %llu bytes", (unsigned long long)MAX_LANE_BYTES);
+        if ((n - 1) > base_bytes / stride) return fail(TPIMD5_EINVAL, "dev_hash_buffers: n*stride runs past base_bytes");
+        aligned = ((uintptr_t)d_base & 15) == 0 && (stride & 15) == 0;
+    }
+    CU(cudaSetDevice(s->dev));
+    LaneArgs a{};
+    a.base = (const uint8_t *)d_base; a.base_bytes = base_bytes;
+    a.off = d_offsets; a.len = d_lengths; a.stride = stride;
+    a.table = (uint4 *)d_digests_out; a.n = n;
+    return launch_lanes(ctx, a, aligned, (cudaStream_t)cuda_stream);
+}
+
+extern "C" uint64_t tpimd5_s3_part_size(uint64_t size, uint64_t chunk_size, uint32_t max_parts) {
+    // [rclone] backend/s3 uploadMultipart: keep chunk_size unless that needs max_parts or more parts
+    if (chunk_size == 0 || max_parts == 0) return 0;
+    uint64_t part = chunk_size;
+    if (size / part >= max_parts) part = (((size / max_parts) >> 20) + 1) << 20;
+    return part;
+}
+
+extern "C" uint32_t tpimd5_s3_nparts(uint64_t size, uint64_t part_size) {
+    if (part_size == 0) return 0;
+    if (size == 0) return 1;
+    uint64_t n = (size + part_size - 1) / part_size;
+    return n > 0xffffffffull ? 0 : (uint32_t)n;
+}
+
+extern "C" int tpimd5_dev_s3_etag(tpimd5_ctx *ctx, int slot, const void *d_data, uint64_t size, uint64_t part_size,
+                                  void *d_part_digests, void *d_etag_md5_out, void *cuda_stream) {
+    Slot *s = get_slot(ctx, slot);
+    if (!s) return fail(TPIMD5_EINVAL, "dev_s3_etag: bad context or slot");
+    if (!d_etag_md5_out || (!d_data && size)) return fail(TPIMD5_EINVAL, "dev_s3_etag: null pointer");
+    if (part_size == 0) return fail(TPIMD5_EINVAL, "dev_s3_etag: part_size 0");
+    if (part_size > MAX_LANE_BYTES) return fail(TPIMD5_ERANGE, "dev_s3_etag: part above %llu bytes", (unsigned long long)MAX_LANE_BYTES);
+    const uint32_t np = tpimd5_s3_nparts(size, part_size);
+    if (!np) return fail(TPIMD5_ERANGE, "dev_s3_etag: too many parts");
+    CU(cudaSetDevice(s->dev));
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    uint8_t *parts = (uint8_t *)d_part_digests;
+    if (!parts) {
+        // library scratch: shared by the slot, so serialise callers that rely on it
+        std::lock_guard<std::mutex> g(s->mu);
+        int rc = ensure_scratch(*s, (size_t)np * 16);
+        if (rc) return rc;
+        parts = s->d_scratch;
+    }
+    if (((uintptr_t)parts & 15) || ((uintptr_t)d_etag_md5_out & 15)) return fail(TPIMD5_EINVAL, "dev_s3_etag: outputs must be 16-byte aligned");
+    // K2: one lane per part
+    LaneArgs a{};
+    a.base = (const uint8_t *)d_data;
+    a.base_bytes = size; a.stride = part_size; a.table = (uint4 *)parts; a.n = np;
+    bool aligned = ((uintptr_t)d_data & 15) == 0 && (part_size & 15) == 0;
+    int rc = launch_lanes(ctx, a, aligned, st);
+    if (rc) return rc;
+    // K2b: digest of digests -- the part digests are one more message of 16*np bytes
+    LaneArgs b{};
+    b.base = parts; b.base_bytes = (uint64_t)np * 16; b.stride = (uint64_t)np * 16;
+    b.table = (uint4 *)d_etag_md5_out; b.n = 1;
+    return launch_lanes(ctx, b, true, st);
+}
+
+// three launches: per-tile counts, exclusive scan of the counts, ordered scatter
+static int diff_launch(tpimd5_ctx *ctx, const void *d_old16, const void *d_new16, size_t n, uint32_t *d_idx,
+                       uint64_t *d_count, uint64_t *tile_counts, cudaStream_t st) {
+    const uint64_t tiles = (n + DIFF_TILE - 1) / DIFF_TILE;
+    diff_tile_kernel<false><<<(unsigned)tiles, DIFF_THREADS, 0, st>>>((const uint4 *)d_old16, (const uint4 *)d_new16, n, tile_counts, nullptr);
+    diff_scan_kernel<<<1, 1024, 0, st>>>(tile_counts, tiles, d_count);
+    diff_tile_kernel<true><<<(unsigned)tiles, DIFF_THREADS, 0, st>>>((const uint4 *)d_old16, (const uint4 *)d_new16, n, tile_counts, d_idx);
+    CU(cudaGetLastError());
+    ctx->launches.fetch_add(3);
+    return 0;
+}
+
+extern "C" int tpimd5_dev_diff(tpimd5_ctx *ctx, int slot, const void *d_old16, const void *d_new16, size_t n,
+                               uint32_t *d_changed_idx_out, uint64_t *d_n_changed_out, void *cuda_stream) {
+    Slot *s = get_slot(ctx, slot);
+    if (!s) return fail(TPIMD5_EINVAL, "dev_diff: bad context or slot");
+    if (!d_n_changed_out) return fail(TPIMD5_EINVAL, "dev_diff: null count pointer");
+    if (n > 0xffffffffull) return fail(TPIMD5_ERANGE, "dev_diff: more than 2^32 units");
+    CU(cudaSetDevice(s->dev));
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    if (n == 0) {
+        CU(cudaMemsetAsync(d_n_changed_out, 0, sizeof(uint64_t), st));
+        return 0;
+    }
+    if (!d_old16 || !d_new16 || !d_changed_idx_out) return fail(TPIMD5_EINVAL, "dev_diff: null pointer");
+    if (((uintptr_t)d_old16 | (uintptr_t)d_new16) & 15) return fail(TPIMD5_EINVAL, "dev_diff: manifests must be 16-byte aligned");
+    uint64_t *counts;
+    {
+        // tile counts live in the slot's scratch, which calls on this slot share
+        std::lock_guard<std::mutex> g(s->mu);
+        int rc = ensure_scratch(*s, ((n + DIFF_TILE - 1) / DIFF_TILE) * sizeof(uint64_t));
+        if (rc) return rc;
+        counts = (uint64_t *)s->d_scratch;
+    }
+    return diff_launch(ctx, d_old16, d_new16, n, d_changed_idx_out, d_n_changed_out, counts, st);
+}
+
+extern "C" int tpimd5_dev_synth_fill(tpimd5_ctx *ctx, int slot, void *d_out, uint64_t seed, uint64_t first_file_index,
+                                     uint64_t file_len, uint64_t n_files, void *cuda_stream) {
+    Slot *s = get_slot(ctx, slot);
+    if (!s) return fail(TPIMD5_EINVAL, "dev_synth_fill: bad context or slot");
+    if (!d_out || ((uintptr_t)d_out & 15)) return fail(TPIMD5_EINVAL, "dev_synth_fill: output must be 16-byte aligned");
+    if (file_len == 0 || (file_len & 15)) return fail(TPIMD5_EINVAL, "dev_synth_fill: file_len must be a positive multiple of 16");
+    if (n_files == 0) return 0;
+    CU(cudaSetDevice(s->dev));
+    const uint64_t total16 = (file_len >> 4) * n_files;
+    const uint64_t want = (total16 + 255) / 256;
+    const unsigned grid = (unsigned)std::min<uint64_t>(want, 148u * 64u);
+    synth_fill_kernel<<<grid, 256, 0, (cudaStream_t)cuda_stream>>>((uint4 *)d_out, seed, first_file_index, file_len, n_files);
+    CU(cudaGetLastError());
+    ctx->launches.fetch_add(1);
+    return 0;
+}
+
+extern "C" int tpimd5_dev_int_probe(tpimd5_ctx *ctx, int slot, int mode, int ctas_per_sm, uint32_t iters, void *d_out,
+                                    uint64_t *blocks_out, void *cuda_stream) {
+    Slot *s = get_slot(ctx, slot);
+    if (!s || !d_out || ctas_per_sm < 1 || ctas_per_sm > 16 || mode < 0 || mode > 3)
+        return fail(TPIMD5_EINVAL, "dev_int_probe: bad argument");
+    CU(cudaSetDevice(s->dev));
+    int sms = 0;
+    CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->dev));
+    const unsigned grid = (unsigned)(sms * ctas_per_sm);
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    switch (mode) {
+        case 0: int_probe_kernel<0><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
+        case 1: int_probe_kernel<1><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
+        case 2: int_probe_kernel<2><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
+        default: int_probe_kernel<3><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
+    }
+    CU(cudaGetLastError());
+    ctx->launches.fetch_add(1);
+    if (blocks_out) *blocks_out = (uint64_t)grid * 128u * iters;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host ingest pipeline
+// ------------------------------------------------------------------------------------------------
+// A job is a list of independent units.  Unit bytes come from memory (base+off) or from a file.
+// Optional per-unit chaining input (streams): starting state, bytes hashed before, and whether
+// to finalise.  Results (digest or chaining value) land in out[16*i].
+struct Job {
+    size_t n = 0;
+    const uint8_t *base = nullptr;
+    const uint64_t *off = nullptr;       // may be null when paths are given
+    const uint64_t *len = nullptr;
+    const char *const *paths = nullptr;
+    const uint64_t *file_off = nullptr;    // with paths: unit i is bytes [file_off[i], +len[i]) of its file (S3 parts)
+    const uint8_t *init_states = nullptr;  // 16*n or null
+    const uint64_t *prior = nullptr;       // or null
+    const uint8_t *nonfinal = nullptr;     // per unit: 1 = leave as chaining value; or null
+    uint8_t *out = nullptr;
+    size_t failed_index = (size_t)-1;
+};
+
+struct Piece {
+    uint32_t unit;      // index into the device's unit list
+    uint64_t src_off;   // bytes of the unit before this piece
+    uint64_t len;
+    uint64_t dst;       // byte offset in the staging buffer
+    bool last;
+};
+
+// Byte-balanced split of units over devices: largest first, each to the least-loaded device
+// (greedy LPT).  Returns per-device unit lists in descending size order, so that a device's
+// longest chain starts first (its latency bounds the device's finish time).
+static void shard_lpt(const uint64_t *len, size_t n, int ndev, std::vector<std::vector<uint32_t>> &out) {
+    out.assign(ndev, {});
+    if (ndev == 1) {
+        out[0].resize(n);
+        for (size_t i = 0; i < n; ++i) out[0][i] = (uint32_t)i;
+        return;
+    }
+    std::vector<uint32_t> order(n);
+    for (size_t i = 0; i < n; ++i) order[i] = (uint32_t)i;
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return len[a] > len[b]; });
+    std::vector<uint64_t> load(ndev, 0);
+    for (uint32_t u : order) {
+        int best = 0;
+        for (int d = 1; d < ndev; ++d)
+            if (load[d] < load[best]) best = d;
+        out[best].push_back(u);
+        load[best] += len[u] + 72;  // padding blocks cost too: keeps runs of empty files spread out
+    }
+}
+
+extern "C" int tpimd5_shard_lpt(const uint64_t *lengths, size_t n, int n_shards, uint32_t *shard_of_out) {
+    if (!lengths || !shard_of_out || n_shards < 1) return fail(TPIMD5_EINVAL, "shard_lpt: bad argument");
+    if (n > 0xffffffffull) return fail(TPIMD5_ERANGE, "shard_lpt: more than 2^32 units");
+    std::vector<std::vector<uint32_t>> sh;
+    shard_lpt(lengths, n, n_shards, sh);
+    for (int d = 0; d < n_shards; ++d)
+        for (uint32_t u : sh[d]) shard_of_out[u] = (uint32_t)d;
+    return 0;
+}
+
+static int read_fully(int fd, uint8_t *dst, uint64_t off, uint64_t n) {
+    while (n) {
+        ssize_t r = pread(fd, dst, n > (1u << 30) ? (1u << 30) : (size_t)n, (off_t)off);
+        if (r < 0) {
+            if (errno == EINTR) continue;
+            return -1;
+        }
+        if (r == 0) return -2;  // shorter than promised
+        dst += r; off += (uint64_t)r; n -= (uint64_t)r;
+    }
+    return 0;
+}
+
+// Runs one device's share of a job.  `units` are indices into the job.
+static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint32_t> &units) {
+    if (units.empty()) return 0;
+    std::lock_guard<std::mutex> guard(s.mu);
+    CU(cudaSetDevice(s.dev));
+    int rc = ensure_staging(ctx, s);
+    if (rc) return rc;
+    rc = ensure_table(s, units.size());
+    if (rc) return rc;
+    const size_t nu = units.size();
+    const bool from_files = job.paths != nullptr;
+
+    // chaining values to start from
+    if (job.init_states) {
+        for (size_t i = 0; i < nu; ++i) memcpy(s.h_table + 16 * i, job.init_states + 16 * (size_t)units[i], 16);
+        CU(cudaMemcpyAsync(s.d_table, s.h_table, nu * 16, cudaMemcpyHostToDevice, s.s_comp));
+    }
+
+    // Direct mode: units already lie close together and in order in caller memory, so each batch is
+    // one H2D copy straight from there (full speed when the caller's buffer is pinned).  Otherwise
+    // (scattered units, files) the pool packs units 16-byte aligned into pinned staging first.
+    bool direct = !from_files;
+    if (direct) {
+        uint64_t bytes = 0;
+        for (size_t i = 0; i < nu && direct; ++i) {
+            const uint32_t u = units[i];
+            if (i && job.off[u] < job.off[units[i - 1]] + job.len[units[i - 1]]) direct = false;
+            bytes += job.len[u];
+        }
+        if (direct) {
+            const uint64_t span = job.off[units[nu - 1]] + job.len[units[nu - 1]] - job.off[units[0]];
+            if (span > bytes + bytes / 4 + (1u << 20)) direct = false;
+        }
+    }
+
+    std::vector<Piece> pieces;
+    std::vector<uint32_t> order;
+    size_t ui = 0;            // next unit
+    uint64_t consumed = 0;    // bytes of units[ui] already planned
+    int batch = 0;
+    std::atomic<int> io_err{0};
+    std::atomic<size_t> io_idx{(size_t)-1};
+
+    while (ui < nu) {
+        const int bi = batch % NBUF;
+        // ---- plan one batch --------------------------------------------------------------------
+        pieces.clear();
+        uint64_t used = 0;       // bytes of staging consumed
+        uint64_t lo = 0;         // direct mode: caller offset of the batch's first byte ...
+        uint64_t shift = 0;      // ... which lands at this staging offset (keeps offsets' alignment mod 16)
+        bool have_lo = false;
+        while (ui < nu && pieces.size() < MAX_BATCH_LANES) {
+            const uint32_t u = units[ui];
+            const uint64_t ulen = job.len[u];
+            const uint64_t rem = ulen - consumed;
+            uint64_t dst;
+            if (direct) {
+                const uint64_t src = job.off[u] + consumed;
+                if (!have_lo) { lo = src; shift = src & 15; have_lo = true; }
+                dst = src - lo + shift;
+            } else {
+                dst = (used + 15) & ~(uint64_t)15;
+            }
+            if (dst > s.stage_bytes) break;
+            const uint64_t space = s.stage_bytes - dst;
+            if (rem <= space) {
+                pieces.push_back({(uint32_t)ui, consumed, rem, dst, true});
+                used = dst + rem;
+                ++ui; consumed = 0;
+            } else if (pieces.empty() || space >= (8u << 20)) {
+                const uint64_t take = space & ~(uint64_t)63;
+                pieces.push_back({(uint32_t)ui, consumed, take, dst, false});
+                used = dst + take;
+                consumed += take;
+                break;
+            } else {
+                break;
+            }
+        }
+        const size_t np = pieces.size();
+
+        // ---- wait until this staging buffer's previous batch has been consumed -----------------
+        if (batch >= NBUF) CU(cudaEventSynchronize(s.ev_done[bi]));
+
+        // ---- lanes, longest first so that a warp's 32 units finish together ---------------------
+        order.resize(np);
+        for (size_t i = 0; i < np; ++i) order[i] = (uint32_t)i;
+        bool ragged = false;
+        for (size_t i = 1; i < np && !ragged; ++i) ragged = (pieces[i].len >> 6) != (pieces[0].len >> 6);
+        if (ragged) std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return pieces[a].len > pieces[b].len; });
+        LaneDesc &h = s.hd[bi];
+        bool aligned = true;
+        for (size_t i = 0; i < np; ++i) {
+            const Piece &p = pieces[order[i]];
+            const uint32_t u = units[p.unit];
+            h.off[i] = p.dst;
+            h.len[i] = p.len;
+            const uint64_t pr = (job.prior ? job.prior[u] : 0) + p.src_off;
+            h.prior[i] = pr;
+            const bool cont = p.src_off > 0 || job.init_states != nullptr;
+            const bool fin = p.last && !(job.nonfinal && job.nonfinal[u]);
+            h.flags[i] = (fin ? LANE_FINAL : 0u) | (cont ? LANE_CONT : 0u);
+            h.oidx[i] = p.unit;
+            aligned = aligned && (p.dst & 15) == 0;
+            if (p.len > MAX_LANE_BYTES) return fail(TPIMD5_ERANGE, "staging above %llu bytes per unit is not supported", (unsigned long long)MAX_LANE_BYTES);
+        }
+
+        // ---- bring the bytes to the device -----------------------------------------------------
+        if (direct) {
+            if (used > shift) CU(cudaMemcpyAsync(s.d_stage[bi] + shift, job.base + lo, used - shift, cudaMemcpyHostToDevice, s.s_copy));
+        } else {
+            uint8_t *stage = s.h_stage[bi];
+            std::function<void(size_t)> fill = [&](size_t i) {
+                const Piece &p = pieces[i];
+                const uint32_t u = units[p.unit];
+                if (!p.len) return;
+                if (from_files) {
+                    int fd = open(job.paths[u], O_RDONLY | O_CLOEXEC);
+                    const uint64_t fo = job.file_off ? job.file_off[u] : 0;
+                    int r = fd < 0 ? -1 : read_fully(fd, stage + p.dst, fo + p.src_off, p.len);
+                    if (fd >= 0 && p.last && r == 0 && !job.file_off) {
+                        // the listing promised exactly job.len[u] bytes: a longer file is a changed file
+                        uint8_t probe;
+                        if (pread(fd, &probe, 1, (off_t)(p.src_off + p.len)) > 0) r = -3;
+                    }
+                    if (fd >= 0) close(fd);
+                    if (r != 0) {
+                        int expect = 0;
+                        if (io_err.compare_exchange_strong(expect, r == -1 ? errno ? errno : EIO : (r == -2 ? -2 : -3))) io_idx = u;
+                    }
+                } else {
+                    memcpy(stage + p.dst, job.base + job.off[u] + p.src_off, p.len);
+                }
+            };
+            // grain: a few MiB of copying or a handful of files per task
+            size_t grain = from_files ? 8 : std::max<size_t>(1, np / (size_t)(8 * (ctx->pool->size() + 1)));
+            if (!from_files && np < 64) grain = 1;
+            ctx->pool->parallel_for(np, grain, fill);
+            if (io_err.load() != 0) break;
+            if (used) CU(cudaMemcpyAsync(s.d_stage[bi], stage, used, cudaMemcpyHostToDevice, s.s_copy));
+        }
+        // descriptors: five arrays, copied as stored (their device mirror has the same carving)
+        CU(cudaMemcpyAsync(s.dd[bi].off, h.off, np * 8, cudaMemcpyHostToDevice, s.s_copy));
+        CU(cudaMemcpyAsync(s.dd[bi].len, h.len, np * 8, cudaMemcpyHostToDevice, s.s_copy));
+        CU(cudaMemcpyAsync(s.dd[bi].prior, h.prior, np * 8, cudaMemcpyHostToDevice, s.s_copy));
+        CU(cudaMemcpyAsync(s.dd[bi].flags, h.flags, np * 4, cudaMemcpyHostToDevice, s.s_copy));
+        CU(cudaMemcpyAsync(s.dd[bi].oidx, h.oidx, np * 4, cudaMemcpyHostToDevice, s.s_copy));
+        CU(cudaEventRecord(s.ev_copied[bi], s.s_copy));
+
+        // ---- hash ------------------------------------------------------------------------------
+        CU(cudaStreamWaitEvent(s.s_comp, s.ev_copied[bi], 0));
+        LaneArgs a{};
+        a.base = s.d_stage[bi]; a.base_bytes = used;
+        a.off = s.dd[bi].off; a.len = s.dd[bi].len; a.prior = s.dd[bi].prior;
+        a.flags = s.dd[bi].flags; a.out_idx = s.dd[bi].oidx;
+        a.table = s.d_table; a.n = np;
+        rc = launch_lanes(ctx, a, aligned, s.s_comp);
+        if (rc) return rc;
+        CU(cudaEventRecord(s.ev_done[bi], s.s_comp));
+        ++batch;
+    }
+
+    if (io_err.load() != 0) {
+        cudaStreamSynchronize(s.s_copy);
+        cudaStreamSynchronize(s.s_comp);
+        const size_t u = io_idx.load();
+        job.failed_index = u;
+        const int e = io_err.load();
+        if (e == -2) return fail(TPIMD5_EIO, "unit %zu (%s): file is shorter than its listed size", u, job.paths[u]);
+        if (e == -3) return fail(TPIMD5_EIO, "unit %zu (%s): file is longer than its listed size", u, job.paths[u]);
+        return fail(TPIMD5_EIO, "unit %zu (%s): %s", u, job.paths[u], strerror(e));
+    }
+
+    // ---- digests home -------------------------------------------------------------------------
+    CU(cudaMemcpyAsync(s.h_table, s.d_table, nu * 16, cudaMemcpyDeviceToHost, s.s_comp));
+    CU(cudaStreamSynchronize(s.s_comp));
+    for (size_t i = 0; i < nu; ++i) memcpy(job.out + 16 * (size_t)units[i], s.h_table + 16 * i, 16);
+    return 0;
+}
+
+static int run_job(tpimd5_ctx *ctx, Job &job) {
+    if (job.n == 0) return 0;
+    if (job.n > 0xffffffffull) return fail(TPIMD5_ERANGE, "more than 2^32 units in one call");
+    const int ndev = (int)ctx->slots.size();
+    std::vector<std::vector<uint32_t>> shards;
+    if (ndev == 1 || job.init_states) {
+        // chained units (streams) stay on device 0: their state lives there between calls
+        shard_lpt(job.len, job.n, 1, shards);
+        return run_device(ctx, *ctx->slots[0], job, shards[0]);
+    }
+    shard_lpt(job.len, job.n, ndev, shards);
+    // direct mode wants ascending addresses; LPT order is by size.  Re-sort each shard by the
+    // caller's order (for files that is listing order, which is also friendliest to the page cache).
+    for (auto &v : shards) std::sort(v.begin(), v.end());
+    std::vector<int> rcs(ndev, 0);
+    std::vector<std::string> errs(ndev);
+    std::vector<std::thread> th;
+    for (int d = 0; d < ndev; ++d)
+        th.emplace_back([&, d] {
+            rcs[d] = run_device(ctx, *ctx->slots[d], job, shards[d]);
+            if (rcs[d]) errs[d] = g_err;
+        });
+    for (auto &t : th) t.join();
+    for (int d = 0; d < ndev; ++d)
+        if (rcs[d]) {
+            g_err = errs[d];
+            return rcs[d];
+        }
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host entry points
+// ------------------------------------------------------------------------------------------------
+extern "C" int tpimd5_hash_buffers(tpimd5_ctx *ctx, const uint8_t *base, const uint64_t *offsets, const uint64_t *lengths,
+                                   size_t n, uint8_t *digests_out) {
+    if (!ctx) return fail(TPIMD5_EINVAL, "hash_buffers: null context");
+    if (n == 0) return 0;
+    if (!offsets || !lengths || !digests_out) return fail(TPIMD5_EINVAL, "hash_buffers: null pointer");
+    Job job;
+    job.n = n; job.base = base; job.off = offsets; job.len = lengths; job.out = digests_out;
+    return run_job(ctx, job);
+}
+
+extern "C" int tpimd5_hash_files(tpimd5_ctx *ctx, const char *const *paths, const uint64_t *sizes, size_t n,
+                                 uint8_t *digests_out, size_t *failed_index_out) {
+    if (failed_index_out) *failed_index_out = (size_t)-1;
+    if (!ctx) return fail(TPIMD5_EINVAL, "hash_files: null context");
+    if (n == 0) return 0;
+    if (!paths || !digests_out) return fail(TPIMD5_EINVAL, "hash_files: null pointer");
+    std::vector<uint64_t> st_sizes;
+    if (!sizes) {
+        st_sizes.resize(n);
+        for (size_t i = 0; i < n; ++i) {
+            struct stat sb;
+            if (stat(paths[i], &sb) != 0) {
+                if (failed_index_out) *failed_index_out = i;
+                return fail(TPIMD5_EIO, "unit %zu (%s): %s", i, paths[i], strerror(errno));
+            }
+            st_sizes[i] = (uint64_t)sb.st_size;
+        }
+        sizes = st_sizes.data();
+    }
+    Job job;
+    job.n = n; job.paths = paths; job.len = sizes; job.out = digests_out;
+    int rc = run_job(ctx, job);
+    if (rc && failed_index_out) *failed_index_out = job.failed_index;
+    return rc;
+}
+
+static int s3_common(tpimd5_ctx *ctx, const uint8_t *data, const char *path, uint64_t size, uint64_t part_size,
+                     uint8_t *part_digests_out, uint8_t etag_md5_out[16], uint32_t *nparts_out) {
+    if (!ctx || !etag_md5_out) return fail(TPIMD5_EINVAL, "s3_etag: null pointer");
+    if (part_size == 0) return fail(TPIMD5_EINVAL, "s3_etag: part_size 0");
+    const uint32_t np = tpimd5_s3_nparts(size, part_size);
+    if (!np) return fail(TPIMD5_ERANGE, "s3_etag: too many parts");
+    std::vector<uint8_t> own;
+    uint8_t *pd = part_digests_out;
+    if (!pd) { own.resize((size_t)np * 16); pd = own.data(); }
+    {
+        std::vector<uint64_t> off(np), len(np);
+        for (uint32_t i = 0; i < np; ++i) {
+            off[i] = (uint64_t)i * part_size;
+            len[i] = std::min(part_size, size - off[i]);
+        }
+        Job job;
+        job.n = np; job.len = len.data(); job.out = pd;
+        std::vector<const char *> same;
+        if (path) {
+            // parts of one file: np units that share a path and differ in file offset
+            struct stat sb;
+            if (stat(path, &sb) != 0) return fail(TPIMD5_EIO, "%s: %s", path, strerror(errno));
+            if ((uint64_t)sb.st_size != size)
+                return fail(TPIMD5_EIO, "%s: size is %llu, not the listed %llu bytes", path, (unsigned long long)sb.st_size,
+                            (unsigned long long)size);
+            same.assign(np, path);
+            job.paths = same.data(); job.file_off = off.data();
+        } else {
+            job.base = data; job.off = off.data();
+        }
+        int rc = run_job(ctx, job);
+        if (rc) return rc;
+    }
+    // digest of digests: one more unit, hashed on the GPU as well
+    const uint64_t zero = 0, dl = (uint64_t)np * 16;
+    Job j2;
+    j2.n = 1; j2.base = pd; j2.off = &zero; j2.len = &dl; j2.out = etag_md5_out;
+    int rc = run_job(ctx, j2);
+    if (rc) return rc;
+    if (nparts_out) *nparts_out = np;
+    return 0;
+}
+
+extern "C" int tpimd5_s3_etag_buffer(tpimd5_ctx *ctx, const uint8_t *data, uint64_t size, uint64_t part_size,
+                                     uint8_t *part_digests_out, uint8_t etag_md5_out[16], uint32_t *nparts_out) {
+    if (!data && size) return fail(TPIMD5_EINVAL, "s3_etag_buffer: null data");
+    return s3_common(ctx, data, nullptr, size, part_size, part_digests_out, etag_md5_out, nparts_out);
+}
+
+extern "C" int tpimd5_s3_etag_file(tpimd5_ctx *ctx, const char *path, uint64_t size, uint64_t part_size,
+                                   uint8_t *part_digests_out, uint8_t etag_md5_out[16], uint32_t *nparts_out) {
+    if (!path) return fail(TPIMD5_EINVAL, "s3_etag_file: null path");
+    return s3_common(ctx, nullptr, path, size, part_size, part_digests_out, etag_md5_out, nparts_out);
+}
+
+extern "C" int tpimd5_diff(tpimd5_ctx *ctx, const uint8_t *old16, const uint8_t *new16, size_t n, uint32_t *changed_idx_out,
+                           size_t *n_changed_out) {
+    if (!ctx || !n_changed_out) return fail(TPIMD5_EINVAL, "diff: null pointer");
+    *n_changed_out = 0;
+    if (n == 0) return 0;
+    if (!old16 || !new16 || !changed_idx_out) return fail(TPIMD5_EINVAL, "diff: null pointer");
+    if (n > 0xffffffffull) return fail(TPIMD5_ERANGE, "diff: more than 2^32 units");
+    Slot &s = *ctx->slots[0];
+    std::lock_guard<std::mutex> guard(s.mu);
+    CU(cudaSetDevice(s.dev));
+    {
+        int rc0 = ensure_scratch(s, ((n + DIFF_TILE - 1) / DIFF_TILE) * sizeof(uint64_t));
+        if (rc0) return rc0;
+    }
+    uint8_t *d_old = nullptr, *d_new = nullptr;
+    uint32_t *d_idx = nullptr;
+    uint64_t *d_cnt = nullptr;
+    int rc = 0;
+    uint64_t cnt = 0;
+    auto cleanup = [&] {
+        if (d_old) cudaFree(d_old);
+        if (d_new) cudaFree(d_new);
+        if (d_idx) cudaFree(d_idx);
+        if (d_cnt) cudaFree(d_cnt);
+    };
+#define CUX(call)                                                                                     \
+    do {                                                                                              \
+        cudaError_t e_ = (call);                                                                      \
+        if (e_ != cudaSuccess) {                                                                      \
+            cleanup();                                                                                \
+            return fail(TPIMD5_ECUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+        }                                                                                             \
+    } while (0)
+    CUX(cudaMalloc(&d_old, n * 16));
+    CUX(cudaMalloc(&d_new, n * 16));
+    CUX(cudaMalloc(&d_idx, n * 4));
+    CUX(cudaMalloc(&d_cnt, 8));
+    CUX(cudaMemcpyAsync(d_old, old16, n * 16, cudaMemcpyHostToDevice, s.s_comp));
+    CUX(cudaMemcpyAsync(d_new, new16, n * 16, cudaMemcpyHostToDevice, s.s_comp));
+    rc = diff_launch(ctx, d_old, d_new, n, d_idx, d_cnt, (uint64_t *)s.d_scratch, s.s_comp);
+    if (rc) { cleanup(); return rc; }
+    CUX(cudaMemcpyAsync(&cnt, d_cnt, 8, cudaMemcpyDeviceToHost, s.s_comp));
+    CUX(cudaStreamSynchronize(s.s_comp));
+    if (cnt) CUX(cudaMemcpy(changed_idx_out, d_idx, cnt * 4, cudaMemcpyDeviceToHost));
+#undef CUX
+    cleanup();
+    *n_changed_out = (size_t)cnt;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// streaming hasher (Go hash.Hash semantics)
+// ------------------------------------------------------------------------------------------------
+struct tpimd5_stream {
+    tpimd5_ctx *ctx = nullptr;
+    uint8_t state[16];          // chaining value after `hashed` bytes
+    uint64_t hashed = 0;        // multiple of 64
+    std::vector<uint8_t> pend;  // bytes written but not hashed yet
+    std::mutex mu;
+};
+
+static const uint8_t MD5_IV_BYTES[16] = {0x01, 0x23, 0x45, 0x67, 0x89, 0xab, 0xcd, 0xef,
+                                         0xfe, 0xdc, 0xba, 0x98, 0x76, 0x54, 0x32, 0x10};
+constexpr size_t STREAM_FLUSH = 4u << 20;  // pending bytes that trigger a launch
+
+extern "C" int tpimd5_stream_open(tpimd5_ctx *ctx, tpimd5_stream **out) {
+    if (!ctx || !out) return fail(TPIMD5_EINVAL, "stream_open: null pointer");
+    auto *s = new tpimd5_stream;
+    s->ctx = ctx;
+    memcpy(s->state, MD5_IV_BYTES, 16);
+    *out = s;
+    return 0;
+}
+
+extern "C" void tpimd5_stream_close(tpimd5_stream *s) { delete s; }
+
+extern "C" int tpimd5_stream_reset(tpimd5_stream *s) {
+    if (!s) return fail(TPIMD5_EINVAL, "stream_reset: null stream");
+    std::lock_guard<std::mutex> g(s->mu);
+    memcpy(s->state, MD5_IV_BYTES, 16);
+    s->hashed = 0;
+    s->pend.clear();
+    return 0;
+}
+
+// Hash the whole blocks pending in each of `ss` in one launch; keeps < 64 bytes per stream.
+static int flush_streams(tpimd5_stream *const *ss, size_t n) {
+    if (n == 0) return 0;
+    tpimd5_ctx *ctx = ss[0]->ctx;
+    std::vector<uint64_t> off, len, prior;
+    std::vector<uint8_t> init, nonfinal, out;
+    std::vector<size_t> who;
+    for (size_t i = 0; i < n; ++i) {
+        const uint64_t full = ss[i]->pend.size() & ~(size_t)63;
+        if (!full) continue;
+        who.push_back(i);
+        off.push_back((uint64_t)(uintptr_t)ss[i]->pend.data());
+        len.push_back(full);
+        prior.push_back(ss[i]->hashed);
+        init.insert(init.end(), ss[i]->state, ss[i]->state + 16);
+        nonfinal.push_back(1);
+    }
+    if (who.empty()) return 0;
+    out.resize(who.size() * 16);
+    Job job;
+    job.n = who.size(); job.base = nullptr; job.off = off.data(); job.len = len.data();
+    job.init_states = init.data(); job.prior = prior.data(); job.nonfinal = nonfinal.data(); job.out = out.data();
+    int rc = run_job(ctx, job);
+    if (rc) return rc;
+    for (size_t k = 0; k < who.size(); ++k) {
+        tpimd5_stream *s = ss[who[k]];
+        memcpy(s->state, out.data() + 16 * k, 16);
+        s->hashed += len[k];
+        s->pend.erase(s->pend.begin(), s->pend.begin() + (ptrdiff_t)len[k]);
+    }
+    return 0;
+}
+
+extern "C" int tpimd5_stream_write(tpimd5_stream *s, const void *p, size_t n) {
+    if (!s || (!p && n)) return fail(TPIMD5_EINVAL, "stream_write: null pointer");
+    std::lock_guard<std::mutex> g(s->mu);
+    const uint8_t *b = (const uint8_t *)p;
+    while (n) {
+        const size_t room = STREAM_FLUSH > s->pend.size() ? STREAM_FLUSH - s->pend.size() : 0;
+        const size_t take = std::min(n, std::max<size_t>(room, 64));
+        s->pend.insert(s->pend.end(), b, b + take);
+        b += take; n -= take;
+        if (s->pend.size() >= STREAM_FLUSH) {
+            tpimd5_stream *one = s;
+            int rc = flush_streams(&one, 1);
+            if (rc) return rc;
+        }
+    }
+    return 0;
+}
+
+extern "C" int tpimd5_stream_write_many(tpimd5_stream *const *streams, const void *const *ptrs, const size_t *lens,
+                                        size_t n_streams) {
+    if (n_streams == 0) return 0;
+    if (!streams || !ptrs || !lens) return fail(TPIMD5_EINVAL, "stream_write_many: null pointer");
+    for (size_t i = 0; i < n_streams; ++i) {
+        if (!streams[i] || (!ptrs[i] && lens[i])) return fail(TPIMD5_EINVAL, "stream_write_many: null entry %zu", i);
+        if (streams[i]->ctx != streams[0]->ctx) return fail(TPIMD5_EINVAL, "stream_write_many: streams of different contexts");
+        for (size_t k = 0; k < i; ++k)
+            if (streams[k] == streams[i]) return fail(TPIMD5_EINVAL, "stream_write_many: stream listed twice");
+    }
+    // append everything, then advance all streams together (one lane each, one launch)
+    for (size_t i = 0; i < n_streams; ++i) {
+        std::lock_guard<std::mutex> g(streams[i]->mu);
+        const uint8_t *b = (const uint8_t *)ptrs[i];
+        streams[i]->pend.insert(streams[i]->pend.end(), b, b + lens[i]);
+    }
+    return flush_streams(streams, n_streams);
+}
+
+extern "C" int tpimd5_stream_sum(tpimd5_stream *s, uint8_t out[16]) {
+    if (!s || !out) return fail(TPIMD5_EINVAL, "stream_sum: null pointer");
+    std::lock_guard<std::mutex> g(s->mu);
+    // finalise a copy: the pending bytes are hashed with padding from the stream's chaining value,
+    // the stream itself keeps state and pending bytes untouched
+    const uint64_t off = (uint64_t)(uintptr_t)s->pend.data(), len = s->pend.size(), prior = s->hashed;
+    static const uint8_t dummy = 0;
+    const uint64_t off_safe = len ? off : (uint64_t)(uintptr_t)&dummy;
+    Job job;
+    job.n = 1; job.base = nullptr; job.off = &off_safe; job.len = &len;
+    job.init_states = s->state; job.prior = &prior; job.out = out;
+    return run_job(s->ctx, job);
+}

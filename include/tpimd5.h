@@ -1,0 +1,145 @@
+/*
+ * tpimd5.h -- C-ABI of the B200-native workdir-checksum path for terraform-provider-iterative.
+ *
+ * This is the boundary a cgo package (`cuda/`) binds.  It replaces the CPU
+ * hashing that TPI reaches through rclone v1.57.0 (go.mod:32) and Go crypto/md5 (go.mod:3) from
+ *   /root/reference/task/common/machine/storage.go:123-159  machine.Transfer -> sync.CopyDir
+ * The reference has no FFI today (CGO_ENABLED=0, Makefile:22,29); each entry point below names
+ * the Go/rclone interface it stands in for.  Citations "[rclone]" are to the un-vendored
+ * module, by package and function name.
+ *
+ * Conventions
+ *   - plain C types only; every function returns 0 on success or a negative TPIMD5_E* code;
+ *     tpimd5_last_error() gives the text for the calling thread's last failure.
+ *   - digests are 16 raw bytes (A,B,C,D little-endian), i.e. Go's [md5.Size]byte.  rclone's
+ *     hash strings are the lowercase hex of these bytes.
+ *   - the caller owns every pointer it passes; nothing is retained after a call returns
+ *     (cgo pointer rule).  The library owns staging memory, streams and device buffers.
+ *   - there is NO CPU fallback: without a usable CUDA device tpimd5_init() fails.
+ *   - a context may be used from many threads at once; calls that share a device queue up.
+ */
+#ifndef TPIMD5_H
+#define TPIMD5_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define TPIMD5_API __attribute__((visibility("default")))
+#else
+#define TPIMD5_API
+#endif
+
+#define TPIMD5_OK        0
+#define TPIMD5_EINVAL   -1   /* bad argument                                              */
+#define TPIMD5_ENODEV   -2   /* no CUDA device / device id out of range                   */
+#define TPIMD5_ECUDA    -3   /* a CUDA call failed; sticky for the context                */
+#define TPIMD5_EIO      -4   /* open/read failed or a file's size changed; see last_error */
+#define TPIMD5_ENOMEM   -5   /* host or device allocation failed                          */
+#define TPIMD5_ERANGE   -6   /* size beyond what the entry point supports                 */
+
+typedef struct tpimd5_ctx tpimd5_ctx;
+typedef struct tpimd5_stream tpimd5_stream;
+
+/* ---- lifecycle ---------------------------------------------------------------------------
+ * No counterpart in the reference (rclone needs no set-up to hash).  `device_ids` == NULL
+ * means devices 0..n_devices-1.  `staging_bytes_per_device` sizes each of the pinned-host /
+ * device staging buffers of the ingest pipeline (0 = default 256 MiB). */
+TPIMD5_API int tpimd5_device_count(void);
+TPIMD5_API int tpimd5_init(const int *device_ids, int n_devices, size_t staging_bytes_per_device, tpimd5_ctx **out);
+TPIMD5_API void tpimd5_destroy(tpimd5_ctx *ctx);
+TPIMD5_API int tpimd5_ctx_devices(const tpimd5_ctx *ctx);
+TPIMD5_API const char *tpimd5_last_error(void);
+TPIMD5_API const char *tpimd5_version(void);
+
+/* ---- batch / manifest --------------------------------------------------------------------
+ * Replaces, for a whole listing at once, [rclone] backend/local Object.Hash(ctx, hash.MD5) ->
+ * fs/hash StreamTypes -> io.Copy -> crypto/md5 digest.Write/Sum, which rclone's 8 checker
+ * goroutines call one file at a time under operations.CheckHashes (reached from
+ * storage.go:158).  Unit i is bytes [offsets[i], offsets[i]+lengths[i]) of `base`
+ * (hash_buffers) or the file paths[i] (hash_files; sizes may be NULL = fstat).  Units are
+ * spread byte-balanced over the context's devices.  digests_out: 16*n bytes. */
+TPIMD5_API int tpimd5_hash_buffers(tpimd5_ctx *ctx, const uint8_t *base, const uint64_t *offsets, const uint64_t *lengths,
+                        size_t n, uint8_t *digests_out);
+TPIMD5_API int tpimd5_hash_files(tpimd5_ctx *ctx, const char *const *paths, const uint64_t *sizes, size_t n,
+                      uint8_t *digests_out, size_t *failed_index_out);
+
+/* ---- S3 multipart ------------------------------------------------------------------------
+ * Replaces [rclone] backend/s3 uploadMultipart's per-chunk md5.Sum(buf) and the final
+ * md5.Sum(md5s) whose hex + "-N" is the expected ETag (backends registered at
+ * storage.go:21).  tpimd5_s3_part_size is rclone's chunk-size growth rule (chunk_size unless
+ * size/chunk_size >= max_parts, then whole MiB above size/max_parts).  part_digests_out may be
+ * NULL; otherwise 16*nparts bytes (each base64-encodes to a part's Content-MD5). */
+TPIMD5_API uint64_t tpimd5_s3_part_size(uint64_t size, uint64_t chunk_size, uint32_t max_parts);
+TPIMD5_API uint32_t tpimd5_s3_nparts(uint64_t size, uint64_t part_size);
+TPIMD5_API int tpimd5_s3_etag_buffer(tpimd5_ctx *ctx, const uint8_t *data, uint64_t size, uint64_t part_size,
+                          uint8_t *part_digests_out, uint8_t etag_md5_out[16], uint32_t *nparts_out);
+TPIMD5_API int tpimd5_s3_etag_file(tpimd5_ctx *ctx, const char *path, uint64_t size, uint64_t part_size,
+                        uint8_t *part_digests_out, uint8_t etag_md5_out[16], uint32_t *nparts_out);
+
+/* ---- streaming hasher --------------------------------------------------------------------
+ * Go hash.Hash as crypto/md5 implements it: Write (any chunking, never fails for lack of
+ * data), Sum (finalises a copy, the stream continues), Reset, Size()==16, BlockSize()==64.
+ * This is what a whole-file Azure/GCS content-MD5 goes through ([rclone] azureblob/gcs
+ * Object.Hash compare against it).  One stream is one MD5 chain, i.e. one GPU lane: use
+ * tpimd5_stream_write_many to advance many streams in a single launch. */
+TPIMD5_API int tpimd5_stream_open(tpimd5_ctx *ctx, tpimd5_stream **out);
+TPIMD5_API int tpimd5_stream_write(tpimd5_stream *s, const void *p, size_t n);
+TPIMD5_API int tpimd5_stream_write_many(tpimd5_stream *const *streams, const void *const *ptrs, const size_t *lens,
+                             size_t n_streams);
+TPIMD5_API int tpimd5_stream_sum(tpimd5_stream *s, uint8_t out[16]);
+TPIMD5_API int tpimd5_stream_reset(tpimd5_stream *s);
+TPIMD5_API void tpimd5_stream_close(tpimd5_stream *s);
+
+/* ---- manifest diff -----------------------------------------------------------------------
+ * Replaces the per-pair `srcHash != dstHash` of [rclone] fs/operations checkHashes for two
+ * whole manifests: indices (ascending) of units whose digests differ. */
+TPIMD5_API int tpimd5_diff(tpimd5_ctx *ctx, const uint8_t *old16, const uint8_t *new16, size_t n, uint32_t *changed_idx_out,
+                size_t *n_changed_out);
+
+/* ---- device-resident variants ------------------------------------------------------------
+ * Same arithmetic on data that already sits in HBM of the context's device `slot`; every
+ * pointer is a device pointer and `cuda_stream` is a cudaStream_t (NULL = default stream).
+ * The calls only enqueue work.  These are what kernel-only throughput is measured through;
+ * the reference has no counterpart (its data is never on a device).
+ *   offsets == NULL: unit i is bytes [i*stride, min((i+1)*stride, base_bytes)) (fixed-size
+ *   files / S3 parts), with lengths ignored. */
+TPIMD5_API int tpimd5_dev_hash_buffers(tpimd5_ctx *ctx, int slot, const void *d_base, uint64_t base_bytes,
+                            const uint64_t *d_offsets, const uint64_t *d_lengths, uint64_t stride, size_t n,
+                            void *d_digests_out, void *cuda_stream);
+TPIMD5_API int tpimd5_dev_s3_etag(tpimd5_ctx *ctx, int slot, const void *d_data, uint64_t size, uint64_t part_size,
+                       void *d_part_digests /* 16*nparts, NULL = library scratch */, void *d_etag_md5_out,
+                       void *cuda_stream);
+TPIMD5_API int tpimd5_dev_diff(tpimd5_ctx *ctx, int slot, const void *d_old16, const void *d_new16, size_t n,
+                    uint32_t *d_changed_idx_out, uint64_t *d_n_changed_out, void *cuda_stream);
+/* Synthetic workdir content generated in HBM: file f (f = first_file_index..) occupies
+ * [ (f-first)*file_len, +file_len ) of d_out; bytes equal the CPU generator's. */
+TPIMD5_API int tpimd5_dev_synth_fill(tpimd5_ctx *ctx, int slot, void *d_out, uint64_t seed, uint64_t first_file_index,
+                          uint64_t file_len, uint64_t n_files, void *cuda_stream);
+
+/* ---- sharding ----------------------------------------------------------------------------
+ * Byte-balanced assignment of units to `n_shards` GPUs (largest first, each to the least
+ * loaded shard).  The library uses it inside one context; a one-process-per-GPU launcher calls
+ * it to decide which rank hashes what.  rclone's counterpart is its fixed pool of 8 checker
+ * goroutines pulling pairs off a channel ([rclone] fs/march, fs/sync pairChecker). */
+TPIMD5_API int tpimd5_shard_lpt(const uint64_t *lengths, size_t n, int n_shards, uint32_t *shard_of_out);
+
+/* ---- tuning / introspection --------------------------------------------------------------
+ * Kernel launches issued by this context so far (bench.py's gpu_launches), and the kernel
+ * variant knob used for sweeps (0 = library default). */
+/* Register-only run of the 64-step MD5 body (no memory traffic): `iters` blocks per thread on
+ * 128*ctas_per_sm threads per SM, d_out needs 16 bytes per thread.  Its blocks/s * 64 B is the
+ * integer-issue ceiling quoted next to HBM bandwidth.  mode = step formulation. */
+TPIMD5_API int tpimd5_dev_int_probe(tpimd5_ctx *ctx, int slot, int mode, int ctas_per_sm, uint32_t iters, void *d_out,
+                                    uint64_t *blocks_out, void *cuda_stream);
+TPIMD5_API uint64_t tpimd5_launch_count(const tpimd5_ctx *ctx);
+TPIMD5_API int tpimd5_set_variant(tpimd5_ctx *ctx, int variant);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TPIMD5_H */
