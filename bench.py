@@ -46,7 +46,7 @@ WORKLOAD = "C2: 1,048,576 files x 4 KiB per GPU, one-lane-per-file MD5 manifest"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--variant", type=int, default=int(os.environ.get("TPIMD5_VARIANT", "0")))
@@ -281,16 +281,23 @@ def main():
             print(json.dumps({"variant": variant, "ms": round(ms, 4), "GBps": round(nbytes / ms / 1e6, 1)}), flush=True)
         probe_out = torch.empty(148 * 16 * 128 * 16, dtype=torch.uint8, device=dev)
         for mode in range(4):
-            for ctas in (2, 4, 8):
+            for ctas in (4, 8):
                 ctx.dev_int_probe(mode, ctas, 64, probe_out, stream=stream)
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
-                blocks = ctx.dev_int_probe(mode, ctas, 4096, probe_out, stream=stream)
-                e1.record()
                 torch.cuda.synchronize()
+                with ClockSampler(local_rank, 0.01) as cs:
+                    e0.record()
+                    blocks = 0
+                    for _ in range(30):
+                        blocks += ctx.dev_int_probe(mode, ctas, 4096, probe_out, stream=stream)
+                    e1.record()
+                    torch.cuda.synchronize()
                 ms = e0.elapsed_time(e1)
+                mhz = cs.summary()["sm_mhz"] or 0
+                cyc = (ms * 1e-3 * mhz * 1e6) * 148 * 4 / (blocks / 32 * 64) if mhz else None
                 print(json.dumps({"probe_mode": mode, "warps_per_sm": ctas * 4, "ms": round(ms, 3),
-                                  "GBps_equiv": round(blocks * 64 / ms / 1e6, 1)}), flush=True)
+                                  "GBps_equiv": round(blocks * 64 / ms / 1e6, 1), "clocks": cs.summary(),
+                                  "cycles_per_step_per_smsp": None if cyc is None else round(cyc, 3)}), flush=True)
         return 0
 
     # ---- kernel-only: W warm-up + K timed steps; 4 GiB of input per step >> 126 MB of L2 ---------
@@ -300,7 +307,7 @@ def main():
     barrier()
     launches0 = ctx.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local_rank) as clocks:
+    with ClockSampler(local_rank, 0.002) as clocks:
         e0.record()
         for _ in range(args.steps):
             step()
@@ -313,15 +320,19 @@ def main():
     kernel_ms_local = e0.elapsed_time(e1) / args.steps            # one lanes-kernel launch per step
 
     # ---- integer-issue ceiling: the same 64-step body, registers only ----------------------------
-    mode = (args.variant // 10) if args.variant else 0
+    # best over the step formulations at full occupancy = what the SM's integer pipes can do at most
     probe_out = torch.empty(148 * 16 * 128 * 16, dtype=torch.uint8, device=dev)
-    ctx.dev_int_probe(mode, 4, 64, probe_out, stream=stream)
-    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    p0.record()
-    probe_blocks = ctx.dev_int_probe(mode, 4, 2048, probe_out, stream=stream)
-    p1.record()
-    torch.cuda.synchronize()
-    int_peak = probe_blocks * 64 / (p0.elapsed_time(p1) * 1e-3) / 1e9
+    int_peak, int_peak_mode = 0.0, None
+    for mode in (0, 1, 2):
+        ctx.dev_int_probe(mode, 8, 64, probe_out, stream=stream)
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        p0.record()
+        probe_blocks = ctx.dev_int_probe(mode, 8, 2048, probe_out, stream=stream)
+        p1.record()
+        torch.cuda.synchronize()
+        g = probe_blocks * 64 / (p0.elapsed_time(p1) * 1e-3) / 1e9
+        if g > int_peak:
+            int_peak, int_peak_mode = g, mode
 
     # ---- end to end through the host-pointer entry point -----------------------------------------
     e2e = None
@@ -379,7 +390,7 @@ def main():
                          "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
                          "kernel": "md5_lanes_kernel", "algorithmic_bytes_per_launch": nbytes,
                          "int_issue_peak_GBps": round(int_peak, 1), "frac_of_int_issue": round(achieved / int_peak, 4),
-                         "int_issue_source": "register-only probe of the same 64-step body, 16 warps/SM, same run"},
+                         "int_issue_source": f"register-only probe of the same 64-step MD5 body (best step formulation: mode {int_peak_mode}), 32 warps/SM, same run"},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks.summary(),
         }
         print(json.dumps(line), flush=True)

@@ -326,11 +326,11 @@ static int launch_cfg(const LaneArgs &a, cudaStream_t st) {
 template <bool ALIGNED, int MODE>
 static int launch_variant(int variant, const LaneArgs &a, cudaStream_t st) {
     switch (variant) {
-        default:
         case 1: return launch_cfg<128, ALIGNED, 4, 4, MODE>(a, st);   // 16 warps/SM, 144 KiB smem/SM
         case 2: return launch_cfg<256, ALIGNED, 4, 3, MODE>(a, st);   // 12 warps/SM, 204 KiB
         case 3: return launch_cfg<64, ALIGNED, 4, 5, MODE>(a, st);    // 20 warps/SM, 100 KiB
-        case 4: return launch_cfg<128, ALIGNED, 4, 5, MODE>(a, st);   // 20 warps/SM, 180 KiB
+        default:
+        case 4: return launch_cfg<128, ALIGNED, 4, 5, MODE>(a, st);   // 20 warps/SM, 180 KiB (default: best measured)
         case 5: return launch_cfg<128, ALIGNED, 4, 3, MODE>(a, st);   // 12 warps/SM
         case 6: return launch_cfg<256, ALIGNED, 2, 6, MODE>(a, st);   // 12 warps/SM in CTAs of 2 warps
     }
