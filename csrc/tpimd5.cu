@@ -1069,3 +1069,58 @@ extern "C" int tpimd5_stream_sum(tpimd5_stream *s, uint8_t out[16]) {
     job.init_states = s->state; job.prior = &prior; job.out = out;
     return run_job(s->ctx, job);
 }
+
+// ------------------------------------------------------------------------------------------------
+// S3 ETag with no allocation at all (see include/tpimd5.h for who needs this and why)
+// ------------------------------------------------------------------------------------------------
+// Scratch for the part digests, carried in the library image: one copy per GPU that loads this
+// module.  In host code the name below is only a handle for the runtime; the kernels need the
+// array's address on the current device, which cudaGetSymbolAddress supplies (once per device).
+static __device__ __align__(256) uint8_t g_noalloc_part_digests[(size_t)TPIMD5_NOALLOC_MAX_PARTS * 16];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static uint8_t *g_noalloc_dev_ptr[NOALLOC_MAX_DEVICES];  // [device] -> device address, null until set up
+static std::mutex g_noalloc_mu;
+
+extern "C" int tpimd5_dev_s3_etag_noalloc(int device, const void *d_data, uint64_t size, uint64_t part_size,
+                                          void *d_etag_md5_out, void *cuda_stream) {
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) return fail(TPIMD5_ENODEV, "s3_etag_noalloc: device %d out of range", device);
+    if (!d_etag_md5_out || (!d_data && size)) return fail(TPIMD5_EINVAL, "s3_etag_noalloc: null pointer");
+    if ((uintptr_t)d_etag_md5_out & 15) return fail(TPIMD5_EINVAL, "s3_etag_noalloc: d_etag_md5_out must be 16-byte aligned");
+    if (part_size == 0) return fail(TPIMD5_EINVAL, "s3_etag_noalloc: part_size 0");
+    if (part_size > MAX_LANE_BYTES) return fail(TPIMD5_ERANGE, "s3_etag_noalloc: part above %llu bytes", (unsigned long long)MAX_LANE_BYTES);
+    const uint64_t np = size == 0 ? 1 : (size + part_size - 1) / part_size;
+    if (np > TPIMD5_NOALLOC_MAX_PARTS)
+        return fail(TPIMD5_ERANGE,
+                    "s3_etag_noalloc: %llu parts, but the built-in scratch holds %d part digests; use a larger part_size "
+                    "(tpimd5_s3_part_size) or tpimd5_dev_s3_etag",
+                    (unsigned long long)np, TPIMD5_NOALLOC_MAX_PARTS);
+    CU(cudaSetDevice(device));
+
+    // set-up, first call on this device: where does the array live on *this* GPU?
+    uint8_t *parts;
+    {
+        std::lock_guard<std::mutex> g(g_noalloc_mu);
+        if (!g_noalloc_dev_ptr[device]) {
+            uint8_t *ptr = nullptr;
+            CU(cudaGetSymbolAddress((void **)&ptr, g_noalloc_part_digests));
+            if (!ptr) return fail(TPIMD5_ECUDA, "s3_etag_noalloc: no device address for the scratch array on device %d", device);
+            g_noalloc_dev_ptr[device] = ptr;
+        }
+        parts = g_noalloc_dev_ptr[device];
+    }
+
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    // per-part MD5s into the built-in array (one lane per part) ...
+    LaneArgs a{};
+    a.base = (const uint8_t *)d_data; a.base_bytes = size; a.stride = part_size;
+    a.table = (uint4 *)parts; a.n = np; a.one = 1u;
+    const bool aligned = ((uintptr_t)d_data & 15) == 0 && (part_size & 15) == 0;
+    int rc = aligned ? launch_cfg<128, true, 4, 5, 0>(a, st) : launch_cfg<128, false, 4, 5, 0>(a, st);
+    if (rc) return rc;
+    // ... then the MD5 of those 16*np bytes, read back from the same array
+    LaneArgs b{};
+    b.base = parts; b.base_bytes = np * 16; b.stride = np * 16;
+    b.table = (uint4 *)d_etag_md5_out; b.n = 1; b.one = 1u;
+    return launch_cfg<128, true, 4, 5, 0>(b, st);
+}

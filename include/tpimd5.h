@@ -121,6 +121,39 @@ TPIMD5_API int tpimd5_dev_diff(tpimd5_ctx *ctx, int slot, const void *d_old16, c
 TPIMD5_API int tpimd5_dev_synth_fill(tpimd5_ctx *ctx, int slot, void *d_out, uint64_t seed, uint64_t first_file_index,
                           uint64_t file_len, uint64_t n_files, void *cuda_stream);
 
+/* ---- S3 ETag for callers that must not allocate ---------------------------------------------
+ * This entry point has no counterpart in the reference.
+ *
+ * Who it is for.  TPI tasks are mostly ML jobs, and a checkpoint hook that wants an ETag often runs
+ * inside the training process itself.  There the framework's memory pool has usually claimed
+ * nearly all of HBM up front, so a cudaMalloc from a library can simply fail; and cudaMalloc /
+ * cudaFree stall every stream of the device while they run, which a step loop cannot afford.
+ * Host programs that run under a fixed device-memory budget (the budget is charged at start-up
+ * and later allocations are refused) are in the same position.  Such callers already own the
+ * input buffer and a 16-byte output; what they cannot supply is the kernel's scratch.
+ *
+ * What it does.  Same result as tpimd5_dev_s3_etag with d_part_digests == NULL -- per-part MD5s,
+ * then the MD5 of their concatenation -- but the part digests go to a fixed array that is part of
+ * the library image (static __device__, 16 * TPIMD5_NOALLOC_MAX_PARTS = 160,000 bytes, present on
+ * every GPU that loads the library, until the process exits).  It takes no context, creates
+ * nothing, and calls no allocator of any kind.  d_data, d_etag_md5_out: device pointers on
+ * `device`; d_etag_md5_out 16-byte aligned; cuda_stream: a cudaStream_t of that device (NULL =
+ * default stream).  The call only enqueues two kernels.
+ *
+ * Limits and rules.
+ *   - at most TPIMD5_NOALLOC_MAX_PARTS parts (S3's own ceiling of 10,000): more is refused with
+ *     TPIMD5_ERANGE before anything is launched.  Pick part_size with tpimd5_s3_part_size.
+ *   - one array per GPU, shared by every call: two calls whose kernels can run at the same time on
+ *     one GPU (different streams, or different host threads) overwrite each other's part digests
+ *     and both ETags are garbage.  Keep such calls on one stream or order them with events.
+ *   - the array keeps the previous call's contents.  Nothing here needs it to start at zero: the
+ *     second kernel reads exactly the 16 * nparts bytes the first kernel of the same call wrote.
+ *   - the first call on each device looks up the array's device address and sets the kernels'
+ *     shared-memory attributes; make that first call before any stream capture begins. */
+#define TPIMD5_NOALLOC_MAX_PARTS 10000
+TPIMD5_API int tpimd5_dev_s3_etag_noalloc(int device, const void *d_data, uint64_t size, uint64_t part_size,
+                                          void *d_etag_md5_out, void *cuda_stream);
+
 /* ---- sharding ----------------------------------------------------------------------------
  * Byte-balanced assignment of units to `n_shards` GPUs (largest first, each to the least
  * loaded shard).  The library uses it inside one context; a one-process-per-GPU launcher calls

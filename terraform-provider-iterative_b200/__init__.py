@@ -16,6 +16,8 @@ from .binding import (  # noqa: F401
     Context,
     Stream,
     TpiMd5Error,
+    NOALLOC_MAX_PARTS,
+    dev_s3_etag_noalloc,
     device_count,
     lib_path,
     load_library,
@@ -26,6 +28,6 @@ from .binding import (  # noqa: F401
 )
 
 __all__ = [
-    "Context", "Stream", "TpiMd5Error", "device_count", "lib_path", "load_library",
+    "Context", "Stream", "TpiMd5Error", "NOALLOC_MAX_PARTS", "dev_s3_etag_noalloc", "device_count", "lib_path", "load_library",
     "s3_etag_text", "s3_nparts", "s3_part_size", "shard_lpt",
 ]

@@ -22,7 +22,7 @@ EXPORTS = [
     "tpimd5_s3_etag_buffer", "tpimd5_s3_etag_file", "tpimd5_stream_open", "tpimd5_stream_write",
     "tpimd5_stream_write_many", "tpimd5_stream_sum", "tpimd5_stream_reset", "tpimd5_stream_close", "tpimd5_diff",
     "tpimd5_dev_hash_buffers", "tpimd5_dev_s3_etag", "tpimd5_dev_diff", "tpimd5_dev_synth_fill",
-    "tpimd5_shard_lpt", "tpimd5_dev_int_probe", "tpimd5_launch_count", "tpimd5_set_variant",
+    "tpimd5_dev_s3_etag_noalloc", "tpimd5_shard_lpt", "tpimd5_dev_int_probe", "tpimd5_launch_count", "tpimd5_set_variant",
 ]
 
 
@@ -71,6 +71,7 @@ def load_library() -> C.CDLL:
         "tpimd5_dev_s3_etag": (i32, [vp, i32, vp, u64, u64, vp, vp, vp]),
         "tpimd5_dev_diff": (i32, [vp, i32, vp, vp, sz, vp, vp, vp]),
         "tpimd5_dev_synth_fill": (i32, [vp, i32, vp, u64, u64, u64, u64, vp]),
+        "tpimd5_dev_s3_etag_noalloc": (i32, [i32, vp, u64, u64, vp, vp]),
         "tpimd5_shard_lpt": (i32, [vp, sz, i32, vp]),
         "tpimd5_dev_int_probe": (i32, [vp, i32, i32, i32, u32, vp, C.POINTER(u64), vp]),
         "tpimd5_launch_count": (u64, [vp]),
@@ -112,6 +113,17 @@ def shard_lpt(lengths, n_shards: int) -> np.ndarray:
     out = np.zeros(ln.size, dtype=np.uint32)
     _check(load_library().tpimd5_shard_lpt(ln.ctypes.data, ln.size, n_shards, out.ctypes.data))
     return out
+
+
+NOALLOC_MAX_PARTS = 10000
+
+
+def dev_s3_etag_noalloc(device: int, d_data, size: int, part_size: int, d_etag, stream=None) -> None:
+    """S3 ETag of device-resident data for callers that may not allocate device memory (a
+    checkpoint hook inside a training process whose memory pool owns the GPU, a host program on
+    a fixed memory budget).  Needs no Context; the part digests go to an array built into the
+    library (at most NOALLOC_MAX_PARTS parts).  Calls that can overlap on one GPU race on it."""
+    _check(load_library().tpimd5_dev_s3_etag_noalloc(device, _ptr(d_data), size, part_size, _ptr(d_etag), _ptr(stream)))
 
 
 def _u8(buf) -> np.ndarray:
