@@ -266,7 +266,7 @@ def main():
         ctx.dev_hash_buffers(data, nbytes, n, digests, stride=flen, stream=stream)
 
     if args.sweep:
-        for variant in [1, 2, 3, 4, 5, 6, 11, 12, 14, 21, 22, 24, 31, 32, 34]:
+        for variant in [0, 4, 44, 202, 242, 244, 0]:
             ctx.set_variant(variant)
             for _ in range(3):
                 step()
@@ -280,8 +280,8 @@ def main():
             ms = e0.elapsed_time(e1) / 10
             print(json.dumps({"variant": variant, "ms": round(ms, 4), "GBps": round(nbytes / ms / 1e6, 1)}), flush=True)
         probe_out = torch.empty(148 * 16 * 128 * 16, dtype=torch.uint8, device=dev)
-        for mode in range(4):
-            for ctas in (4, 8):
+        for mode in range(7):
+            for ctas in (4, 5, 8):
                 ctx.dev_int_probe(mode, ctas, 64, probe_out, stream=stream)
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 torch.cuda.synchronize()
@@ -299,6 +299,22 @@ def main():
                                   "GBps_equiv": round(blocks * 64 / ms / 1e6, 1), "clocks": cs.summary(),
                                   "cycles_per_step_per_smsp": None if cyc is None else round(cyc, 3)}), flush=True)
         return 0
+
+    # ---- integer-issue ceiling: the same 64-step body, registers only ----------------------------
+    # best over the step formulations at full occupancy = what the SM's integer pipes can do at most;
+    # taken before the timed steps, on a GPU that is not yet held back by the power cap
+    probe_out = torch.empty(148 * 16 * 128 * 16, dtype=torch.uint8, device=dev)
+    int_peak, int_peak_mode = 0.0, None
+    for mode in (4, 5, 6):
+        ctx.dev_int_probe(mode, 8, 64, probe_out, stream=stream)
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        p0.record()
+        probe_blocks = ctx.dev_int_probe(mode, 8, 2048, probe_out, stream=stream)
+        p1.record()
+        torch.cuda.synchronize()
+        g = probe_blocks * 64 / (p0.elapsed_time(p1) * 1e-3) / 1e9
+        if g > int_peak:
+            int_peak, int_peak_mode = g, mode
 
     # ---- kernel-only: W warm-up + K timed steps; 4 GiB of input per step >> 126 MB of L2 ---------
     args.warmup = max(args.warmup, 3)          # timing rule: at least 3 warm-up steps
@@ -318,21 +334,6 @@ def main():
     ms_step = ms_total / args.steps
     value = world * nbytes / (ms_step * 1e-3) / 1e9
     kernel_ms_local = e0.elapsed_time(e1) / args.steps            # one lanes-kernel launch per step
-
-    # ---- integer-issue ceiling: the same 64-step body, registers only ----------------------------
-    # best over the step formulations at full occupancy = what the SM's integer pipes can do at most
-    probe_out = torch.empty(148 * 16 * 128 * 16, dtype=torch.uint8, device=dev)
-    int_peak, int_peak_mode = 0.0, None
-    for mode in (0, 1, 2):
-        ctx.dev_int_probe(mode, 8, 64, probe_out, stream=stream)
-        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        p0.record()
-        probe_blocks = ctx.dev_int_probe(mode, 8, 2048, probe_out, stream=stream)
-        p1.record()
-        torch.cuda.synchronize()
-        g = probe_blocks * 64 / (p0.elapsed_time(p1) * 1e-3) / 1e9
-        if g > int_peak:
-            int_peak, int_peak_mode = g, mode
 
     # ---- end to end through the host-pointer entry point -----------------------------------------
     e2e = None
@@ -388,7 +389,7 @@ def main():
                        "kernel_variant": args.variant, "sharding": "independent shard per rank, no collective"},
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                          "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
-                         "kernel": "md5_lanes_kernel", "algorithmic_bytes_per_launch": nbytes,
+                         "kernel": "md5_strided_tma_kernel (K1, one lane per file, TMA-fed)", "algorithmic_bytes_per_launch": nbytes,
                          "int_issue_peak_GBps": round(int_peak, 1), "frac_of_int_issue": round(achieved / int_peak, 4),
                          "int_issue_source": f"register-only probe of the same 64-step MD5 body (best step formulation: mode {int_peak_mode}), 32 warps/SM, same run"},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks.summary(),

@@ -44,10 +44,33 @@ __device__ __forceinline__ uint32_t mad1(uint32_t a, uint32_t one, uint32_t c) {
     return r;
 }
 
+//   MODE 4  like 1, but m+k as a plain add hidden from the optimiser (VIADD reg+imm: one register read)
+//   MODE 5  like 3, with the multiplier 1 read from the constant bank instead of a register
+//   MODE 6  steps alternate between 4 and 5
+__constant__ uint32_t c_one = 1u;
+
+__device__ __forceinline__ uint32_t add_imm(uint32_t a, uint32_t k) {
+    uint32_t r;
+    asm("add.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(k));
+    return r;
+}
+__device__ __forceinline__ uint32_t madc(uint32_t a, uint32_t c) {
+    uint32_t r;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(c_one), "r"(c));
+    return r;
+}
+
 template <int MODE, int STEP_PARITY>
 __device__ __forceinline__ uint32_t step_sum(uint32_t a, uint32_t f, uint32_t m, uint32_t k, uint32_t one) {
     if (MODE == 0) {
         return (a + (m + k)) + f;
+    } else if (MODE == 4 || (MODE == 6 && STEP_PARITY == 0)) {
+        const uint32_t x = add_imm(m, k);
+        return a + x + f;
+    } else if (MODE == 5 || MODE == 6) {
+        const uint32_t x = add_imm(m, k);
+        const uint32_t y = madc(a, x);
+        return madc(f, y);
     } else if (MODE == 1 || (MODE == 2 && STEP_PARITY == 0)) {
         const uint32_t x = mad1(m, one, k);
         return a + x + f;

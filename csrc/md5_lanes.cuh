@@ -62,6 +62,27 @@ struct LaneCfg {
     static_assert(CH == 64 || CH == 128 || CH == 256 || CH == 512, "CH");
 };
 
+// The 16 message words of one block from this thread's shared-memory row.  Aligned units: four
+// LDS.128.  Unaligned units: 17 words from the 4-byte boundary below, realigned by funnel shifts.
+template <bool ALIGNED>
+__device__ __forceinline__ void load_block_words(uint32_t src, uint32_t sh, uint32_t (&m)[16]) {
+    if (ALIGNED) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(m[4 * q]), "=r"(m[4 * q + 1]), "=r"(m[4 * q + 2]), "=r"(m[4 * q + 3])
+                         : "r"(src + 16u * q));
+    } else {
+        uint32_t w[17];
+        const uint32_t a0 = src + (sh & ~3u);
+#pragma unroll
+        for (int q = 0; q < 17; ++q) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w[q]) : "r"(a0 + 4u * q));
+        const uint32_t bs = (sh & 3u) * 8u;
+#pragma unroll
+        for (int q = 0; q < 16; ++q) m[q] = __funnelshift_r(w[q], w[q + 1], bs);
+    }
+}
+
 template <int CH, bool ALIGNED, int WARPS, int MINB, int MODE>
 __global__ void __launch_bounds__(WARPS * 32, MINB) md5_lanes_kernel(const LaneArgs p) {
     using Cfg = LaneCfg<CH, ALIGNED, WARPS>;
@@ -144,14 +165,57 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) md5_lanes_kernel(const LaneA
         }
     };
 
+    // the same copy without the per-row predicates, for stages in which every row is full
+    auto issue_full = [&](uint32_t s) {
+        const uint32_t sb = (s & 1u) * Cfg::STAGE_BYTES;
+#pragma unroll
+        for (int k = 0; k < SEGS; ++k) {
+            cp_async16(dst0 + sb + k * (RPI * ROWB), gsrc[k]);
+            gsrc[k] += CH;
+            gleft[k] -= SEGS;
+        }
+        if (!ALIGNED) {
+            cp_async16(xdst0 + sb, xsrc);
+            xsrc += CH;
+            xleft -= SEGS;
+        }
+    };
+
     if (warp_nst > 0) issue(0);
     cp_async_commit();
 
     const uint32_t myrow = wbase + lane * ROWB;
     const uint64_t total = prior + len;
 
+    // ---- phase A: stages in which all 32 units still have CH whole bytes -----------------------
+    // No tail logic, no per-thread predicates: copy, wait, 4 x LDS.128 and the 64 steps per block.
+    // (An unaligned unit needs CH+16 bytes for its shifted window, hence the "+ sh" below.)
+    const uint64_t full64 = (ALIGNED ? len : (len > sh ? len - sh : 0)) / CH;
+    const uint32_t full_st = full64 > 0xffffffffull ? 0xffffffffu : (uint32_t)full64;
+    const uint32_t warp_fast = __reduce_min_sync(0xffffffffu, ALIGNED ? full_st : (full_st ? full_st - 1 : 0));
+    uint32_t s_done = 0;
 #pragma unroll 1
-    for (uint32_t b = 0; b < warp_nb; ++b) {
+    for (; s_done < warp_fast; ++s_done) {
+        const uint32_t s = s_done;
+        if (s + 1 < warp_fast) issue_full(s + 1);
+        else if (s + 1 < warp_nst) issue(s + 1);
+        cp_async_commit();
+        cp_async_wait<1>();
+        __syncwarp();
+        const uint32_t src0 = myrow + (s & 1u) * Cfg::STAGE_BYTES;
+#pragma unroll 1
+        for (uint32_t j = 0; j < (uint32_t)BPS; ++j) {
+            uint32_t m[16];
+            const uint32_t src = src0 + j * 64u;
+            load_block_words<ALIGNED>(src, sh, m);
+            md5_block<MODE>(st, m, p.one);
+        }
+        __syncwarp();
+    }
+
+    // ---- phase B: ragged rest -- tails, padding blocks, units that have already finished --------
+#pragma unroll 1
+    for (uint32_t b = warp_fast * BPS; b < warp_nb; ++b) {
         const uint32_t j = b % BPS, s = b / BPS;
         if (j == 0 && s < warp_nst) {
             if (s + 1 < warp_nst) issue(s + 1);
@@ -163,21 +227,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) md5_lanes_kernel(const LaneA
             uint32_t m[16];
             if (b <= bm && b < nst * BPS) {
                 const uint32_t src = myrow + (s & 1u) * Cfg::STAGE_BYTES + j * 64u;
-                if (ALIGNED) {
-#pragma unroll
-                    for (int q = 0; q < 4; ++q)
-                        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
-                                     : "=r"(m[4 * q]), "=r"(m[4 * q + 1]), "=r"(m[4 * q + 2]), "=r"(m[4 * q + 3])
-                                     : "r"(src + 16u * q));
-                } else {
-                    uint32_t w[17];
-                    const uint32_t a0 = src + (sh & ~3u);
-#pragma unroll
-                    for (int q = 0; q < 17; ++q) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w[q]) : "r"(a0 + 4u * q));
-                    const uint32_t bs = (sh & 3u) * 8u;
-#pragma unroll
-                    for (int q = 0; q < 16; ++q) m[q] = __funnelshift_r(w[q], w[q + 1], bs);
-                }
+                load_block_words<ALIGNED>(src, sh, m);
             } else {
 #pragma unroll
                 for (int q = 0; q < 16; ++q) m[q] = 0;
@@ -190,6 +240,37 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) md5_lanes_kernel(const LaneA
     cp_async_wait<0>();
     if (valid) p.table[oidx] = make_uint4(st[0], st[1], st[2], st[3]);
 }
+
+// ---------------------------------------------------------------------------------------------
+// mbarrier / async-proxy helpers shared with the tensor-map kernel (md5_strided_tma.cuh).
+// (A variant of the kernel above in which every thread fetched its own row with one
+// cp.async.bulk per stage was measured and dropped: one TMA request per 64-256 bytes tops out at
+// 2.3-3.8 TB/s on C2, see profiles/r1_sweep_bulk_per_row.jsonl.)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint32_t mbar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t mbar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(mbar), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t mbar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(mbar)
+                 : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // ---------------------------------------------------------------------------------------------
 // Register-only probe: the same 64-step body with no memory traffic at all.  Its throughput is the

@@ -30,6 +30,7 @@
 
 #include "aux_kernels.cuh"
 #include "md5_lanes.cuh"
+#include "md5_strided_tma.cuh"
 
 using namespace tpimd5;
 
@@ -294,7 +295,7 @@ extern "C" void tpimd5_destroy(tpimd5_ctx *ctx) {
 extern "C" int tpimd5_ctx_devices(const tpimd5_ctx *ctx) { return ctx ? (int)ctx->slots.size() : 0; }
 extern "C" uint64_t tpimd5_launch_count(const tpimd5_ctx *ctx) { return ctx ? ctx->launches.load() : 0; }
 extern "C" int tpimd5_set_variant(tpimd5_ctx *ctx, int variant) {
-    if (!ctx || variant < 0 || variant > 39 || variant % 10 > 6) return fail(TPIMD5_EINVAL, "tpimd5_set_variant: 10*mode(0..3) + shape(0..6)");
+    if (!ctx || variant < 0 || variant > 299) return fail(TPIMD5_EINVAL, "tpimd5_set_variant: 100*loader(0 cp.async, 1 bulk, 2 tensor map for strided units) + 10*mode(0,4,6) + shape");
     ctx->variant = variant;
     return 0;
 }
@@ -330,37 +331,136 @@ static int launch_variant(int variant, const LaneArgs &a, cudaStream_t st) {
         case 2: return launch_cfg<256, ALIGNED, 4, 3, MODE>(a, st);   // 12 warps/SM, 204 KiB
         case 3: return launch_cfg<64, ALIGNED, 4, 5, MODE>(a, st);    // 20 warps/SM, 100 KiB
         default:
-        case 4: return launch_cfg<128, ALIGNED, 4, 5, MODE>(a, st);   // 20 warps/SM, 180 KiB (default: best measured)
-        case 5: return launch_cfg<128, ALIGNED, 4, 3, MODE>(a, st);   // 12 warps/SM
-        case 6: return launch_cfg<256, ALIGNED, 2, 6, MODE>(a, st);   // 12 warps/SM in CTAs of 2 warps
+        case 4: return launch_cfg<128, ALIGNED, 4, 5, MODE>(a, st);   // 20 warps/SM, 180 KiB (default)
+        case 7: return launch_cfg<64, ALIGNED, 4, 8, MODE>(a, st);    // 32 warps/SM, 64 regs, 160 KiB
+        case 9: return launch_cfg<128, ALIGNED, 4, 6, MODE>(a, st);   // 24 warps/SM, 80 regs, 216 KiB
     }
 }
 
-// variant = 10*mode + shape; `aligned`: every unit starts on a 16-byte boundary of device memory.
+// ---- TMA path for equal-sized units at a fixed stride (md5_strided_tma.cuh) -----------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+    static std::once_flag once;
+    static EncodeTiledFn fn = nullptr;
+    std::call_once(once, [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+    });
+    return fn;
+}
+
+// Can this strided launch go through the tensor-map kernel?
+static bool tma_eligible(const void *base, uint64_t stride, uint64_t unit_len, uint64_t n) {
+    return ((uintptr_t)base & 15) == 0 && (stride & 15) == 0 && stride < ((uint64_t)1 << 40) && unit_len >= 1 &&
+           unit_len <= stride && unit_len <= ((uint64_t)1 << 31) && n >= 1 && n <= ((uint64_t)1 << 31) && encode_tiled_fn() != nullptr;
+}
+
+template <int WARPS, int MINB, int NSTAGE, int MODE>
+static int launch_tma_cfg(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len, uint4 *table, cudaStream_t st) {
+    using Cfg = StridedCfg<WARPS, NSTAGE>;
+    auto kern = md5_strided_tma_kernel<WARPS, MINB, NSTAGE, MODE>;
+    static thread_local int configured_dev = -1;
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    if (configured_dev != dev) {
+        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+        CU(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        configured_dev = dev;
+    }
+    const uint64_t per_cta = WARPS * 32;
+    const uint64_t grid = (n + per_cta - 1) / per_cta;
+    kern<<<(unsigned)grid, WARPS * 32, Cfg::SMEM_BYTES, st>>>(tmap, n, unit_len, table, 1u);
+    CU(cudaGetLastError());
+    return 0;
+}
+
+// n units of unit_len bytes, unit u at base + u*stride.  shape: 1..4, mode 0 or 4.
+static int launch_strided_tma(tpimd5_ctx *ctx, const void *base, uint64_t stride, uint64_t unit_len, uint64_t n, uint4 *table,
+                              int shape, int mode, cudaStream_t st) {
+    CUtensorMap tmap;
+    const cuuint64_t gdim[2] = {unit_len, n};
+    const cuuint64_t gstride[1] = {stride};
+    const cuuint32_t box[2] = {128, 32};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult r = encode_tiled_fn()(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(base), gdim, gstride, box, estr,
+                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(TPIMD5_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    int rc;
+#define TPI_TMA(M)                                                                          \
+    switch (shape) {                                                                        \
+        case 1: rc = launch_tma_cfg<4, 4, 3, M>(tmap, n, (uint32_t)unit_len, table, st); break;  \
+        default:                                                                                 \
+        case 2: rc = launch_tma_cfg<4, 5, 2, M>(tmap, n, (uint32_t)unit_len, table, st); break;  \
+        case 3: rc = launch_tma_cfg<4, 3, 4, M>(tmap, n, (uint32_t)unit_len, table, st); break;  \
+        case 4: rc = launch_tma_cfg<4, 6, 2, M>(tmap, n, (uint32_t)unit_len, table, st); break;  \
+    }
+    if (mode == 0) {
+        TPI_TMA(0)
+    } else {
+        TPI_TMA(4)
+    }
+#undef TPI_TMA
+    if (rc == 0) ctx->launches.fetch_add(1);
+    return rc;
+}
+
+// Kernel choice.  variant 0 = library default.  Otherwise 100*loader + 10*mode + shape, where loader
+// 0 forces the cp.async kernel everywhere and 2 allows the tensor-map kernel for strided units.
+static void decode_variant(int v, int &loader, int &mode, int &shape) {
+    if (v == 0) { loader = 2; mode = 4; shape = 0; return; }
+    loader = v / 100; mode = (v / 10) % 10; shape = v % 10;
+}
+
+// `aligned`: every unit starts on a 16-byte boundary of device memory.
 static int launch_lanes(tpimd5_ctx *ctx, const LaneArgs &a0, bool aligned, cudaStream_t st) {
     if (a0.n == 0) return 0;
     LaneArgs a = a0;
     a.one = 1u;
-    const int v = ctx->variant.load();
-    const int shape = v % 10, mode = v / 10;
+    int loader, mode, shape;
+    decode_variant(ctx->variant.load(), loader, mode, shape);
     int rc;
     if (aligned) {
         switch (mode) {
-            default: rc = launch_variant<true, 0>(shape, a, st); break;
-            case 1: rc = launch_variant<true, 1>(shape, a, st); break;
-            case 2: rc = launch_variant<true, 2>(shape, a, st); break;
-            case 3: rc = launch_variant<true, 3>(shape, a, st); break;
+            case 0: rc = launch_variant<true, 0>(shape, a, st); break;
+            default: rc = launch_variant<true, 4>(shape, a, st); break;
+            case 6: rc = launch_variant<true, 6>(shape, a, st); break;
         }
     } else {
         switch (mode) {
-            default: rc = launch_variant<false, 0>(shape, a, st); break;
-            case 1: rc = launch_variant<false, 1>(shape, a, st); break;
-            case 2: rc = launch_variant<false, 2>(shape, a, st); break;
-            case 3: rc = launch_variant<false, 3>(shape, a, st); break;
+            case 0: rc = launch_variant<false, 0>(shape, a, st); break;
+            default: rc = launch_variant<false, 4>(shape, a, st); break;
+            case 6: rc = launch_variant<false, 6>(shape, a, st); break;
         }
     }
     if (rc == 0) ctx->launches.fetch_add(1);
     return rc;
+}
+
+// Units of `stride` bytes back to back: unit i = [i*stride, min((i+1)*stride, base_bytes)).  Whole
+// units go through the tensor-map kernel when the layout allows it, a ragged last unit (and any
+// layout TMA cannot describe) through the general kernel.
+static int launch_strided(tpimd5_ctx *ctx, const void *base, uint64_t base_bytes, uint64_t stride, uint64_t n, uint4 *table,
+                          cudaStream_t st) {
+    if (n == 0) return 0;
+    LaneArgs a{};
+    a.base = (const uint8_t *)base; a.base_bytes = base_bytes; a.stride = stride; a.table = table; a.n = n;
+    const bool aligned = ((uintptr_t)base & 15) == 0 && (stride & 15) == 0;
+    int loader, mode, shape;
+    decode_variant(ctx->variant.load(), loader, mode, shape);
+    const uint64_t n_full = std::min<uint64_t>(n, base_bytes / stride);
+    if (loader == 2 && n_full && tma_eligible(base, stride, stride, n_full)) {
+        int rc = launch_strided_tma(ctx, base, stride, stride, n_full, table, shape, mode, st);
+        if (rc || n_full == n) return rc;
+        a.base += n_full * stride; a.base_bytes -= n_full * stride; a.table += n_full; a.n = n - n_full;
+    }
+    return launch_lanes(ctx, a, aligned, st);
 }
 
 static Slot *get_slot(tpimd5_ctx *ctx, int slot) {
@@ -394,6 +494,7 @@ extern "C" int tpimd5_dev_hash_buffers(tpimd5_ctx *ctx, int slot, const void *d_
     a.base = (const uint8_t *)d_base; a.base_bytes = base_bytes;
     a.off = d_offsets; a.len = d_lengths; a.stride = stride;
     a.table = (uint4 *)d_digests_out; a.n = n;
+    if (!d_offsets) return launch_strided(ctx, d_base, base_bytes, stride, n, (uint4 *)d_digests_out, (cudaStream_t)cuda_stream);
     return launch_lanes(ctx, a, aligned, (cudaStream_t)cuda_stream);
 }
 
@@ -433,11 +534,7 @@ extern "C" int tpimd5_dev_s3_etag(tpimd5_ctx *ctx, int slot, const void *d_data,
     }
     if (((uintptr_t)parts & 15) || ((uintptr_t)d_etag_md5_out & 15)) return fail(TPIMD5_EINVAL, "dev_s3_etag: outputs must be 16-byte aligned");
     // K2: one lane per part
-    LaneArgs a{};
-    a.base = (const uint8_t *)d_data;
-    a.base_bytes = size; a.stride = part_size; a.table = (uint4 *)parts; a.n = np;
-    bool aligned = ((uintptr_t)d_data & 15) == 0 && (part_size & 15) == 0;
-    int rc = launch_lanes(ctx, a, aligned, st);
+    int rc = launch_strided(ctx, d_data, size, part_size, np, (uint4 *)parts, st);
     if (rc) return rc;
     // K2b: digest of digests -- the part digests are one more message of 16*np bytes
     LaneArgs b{};
@@ -503,7 +600,7 @@ extern "C" int tpimd5_dev_synth_fill(tpimd5_ctx *ctx, int slot, void *d_out, uin
 extern "C" int tpimd5_dev_int_probe(tpimd5_ctx *ctx, int slot, int mode, int ctas_per_sm, uint32_t iters, void *d_out,
                                     uint64_t *blocks_out, void *cuda_stream) {
     Slot *s = get_slot(ctx, slot);
-    if (!s || !d_out || ctas_per_sm < 1 || ctas_per_sm > 16 || mode < 0 || mode > 3)
+    if (!s || !d_out || ctas_per_sm < 1 || ctas_per_sm > 16 || mode < 0 || mode > 6)
         return fail(TPIMD5_EINVAL, "dev_int_probe: bad argument");
     CU(cudaSetDevice(s->dev));
     int sms = 0;
@@ -514,7 +611,10 @@ extern "C" int tpimd5_dev_int_probe(tpimd5_ctx *ctx, int slot, int mode, int cta
         case 0: int_probe_kernel<0><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
         case 1: int_probe_kernel<1><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
         case 2: int_probe_kernel<2><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
-        default: int_probe_kernel<3><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
+        case 3: int_probe_kernel<3><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
+        case 4: int_probe_kernel<4><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
+        case 5: int_probe_kernel<5><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
+        default: int_probe_kernel<6><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
     }
     CU(cudaGetLastError());
     ctx->launches.fetch_add(1);
