@@ -55,6 +55,9 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--sweep", action="store_true", help="print kernel-only GB/s for every kernel variant, then exit")
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c5"],
+                    help="c2 = the headline line (default); c3 = S3 ETag of 8 x 64 GiB files, 8 MiB parts (strong scaling); "
+                         "c5 = 100 GiB manifest rebuild + diff.  c3/c5 print kernel-only lines for the record")
     return ap.parse_args()
 
 
@@ -215,6 +218,70 @@ def run_reference(args, rank, world):
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
+def run_side_workload(args, torch, dist, tpi, ctx, dev, rank, world, barrier, max_over_ranks, stream):
+    """Kernel-only lines for BASELINE configs 3 and 5 (not the headline; same JSON shape, fewer keys)."""
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    peak = float(json.load(open(peaks_path))["hbm_gbs"]) if os.path.exists(peaks_path) else 6650.0
+    if args.workload == "c3":
+        size, part, files = 64 << 30, 8 << 20, 8
+        mine = [f for f in range(files) if f % world == rank]
+        data = torch.empty(size, dtype=torch.uint8, device=dev)
+        ctx.dev_synth_fill(data, 3, rank, size, 1, stream=stream)
+        nparts = tpi.s3_nparts(size, part)
+        parts = torch.empty((nparts, 16), dtype=torch.uint8, device=dev)
+        etag = torch.empty(16, dtype=torch.uint8, device=dev)
+
+        def step():
+            for _ in mine:                      # the same resident 64 GiB stands in for each of this rank's files
+                ctx.dev_s3_etag(data, size, part, etag, d_part_digests=parts, stream=stream)
+        work_bytes, label = files * size, "C3: 8 files x 64 GiB, S3 multipart ETag, 8 MiB parts (8,192 lanes per file + digest of digests)"
+        scaling = "strong"
+    else:
+        n, flen = 25600, 4 << 20
+        n_local = n // world
+        data = torch.empty(n_local * flen, dtype=torch.uint8, device=dev)
+        ctx.dev_synth_fill(data, 5, rank * n_local, flen, n_local, stream=stream)
+        old = torch.empty((n_local, 16), dtype=torch.uint8, device=dev)
+        new = torch.empty((n_local, 16), dtype=torch.uint8, device=dev)
+        ctx.dev_hash_buffers(data, n_local * flen, n_local, old, stride=flen, stream=stream)
+        torch.cuda.synchronize()
+        g = torch.Generator(device="cpu").manual_seed(5 + rank)
+        victims = torch.randperm(n_local, generator=g)[: n_local // 20].to(dev)
+        data[victims * flen + 4321] ^= 1
+        idx = torch.empty(n_local, dtype=torch.int32, device=dev)
+        cnt = torch.zeros(1, dtype=torch.int64, device=dev)
+
+        def step():
+            ctx.dev_hash_buffers(data, n_local * flen, n_local, new, stride=flen, stream=stream)
+            ctx.dev_diff(old, new, n_local, idx, cnt, stream=stream)
+        work_bytes, label = n * flen, "C5: 25,600 files x 4 MiB = 100 GiB, 5% mutated: manifest rebuild + digest diff"
+        scaling = "strong"
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    l0 = ctx.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(dev.index or 0, 0.002) as clocks:
+        e0.record()
+        for _ in range(args.steps):
+            step()
+        e1.record()
+        barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    if args.workload == "c5":
+        assert int(cnt.item()) == n_local // 20, "diff did not return exactly the mutated files"
+    if rank == 0:
+        value = work_bytes / (ms * 1e-3) / 1e9
+        print(json.dumps({
+            "metric": METRIC, "value": round(value, 3), "unit": "GB/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": scaling,
+            "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": label, "l2": "inputs far larger than L2", "kernel_variant": args.variant},
+            "roofline": {"bound": "hbm", "achieved": round(value / world, 1), "peak": peak, "unit": "GB/s",
+                         "frac": round(value / world / peak, 4), "traffic": None},
+            "gpu_launches": int(ctx.launch_count() - l0), "clocks": clocks.summary()}), flush=True)
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -256,6 +323,13 @@ def main():
     if args.variant:
         ctx.set_variant(args.variant)
     stream = torch.cuda.current_stream().cuda_stream
+
+    if args.workload != "c2":
+        run_side_workload(args, torch, dist, tpi, ctx, dev, rank, world, barrier, max_over_ranks, stream)
+        ctx.close()
+        if use_dist:
+            dist.destroy_process_group()
+        return 0
 
     data = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     digests = torch.empty((n, 16), dtype=torch.uint8, device=dev)

@@ -65,9 +65,11 @@ md5_strided_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uin
     const uint32_t bm = unit_len >> 6;                        // block that takes the 0x80 marker
     const uint32_t nb = ((unit_len + 8u) >> 6) + 1u;          // blocks incl. padding
 
-    auto fetch = [&](uint32_t s) {                            // lane 0 only
+    // Lane 0 only.  The buffer being refilled was last read by the warp before the __syncwarp that
+    // precedes this call, and those reads have completed (their values were consumed by the MD5
+    // steps), so the TMA write cannot overtake them; no proxy fence is needed for this direction.
+    auto fetch = [&](uint32_t s) {
         const uint32_t buf = s % NSTAGE;
-        fence_proxy_async();
         mbar_expect_tx(mbar0 + 8u * buf, Cfg::STAGE_BYTES);
         tma_load_2d(wbase + buf * Cfg::STAGE_BYTES, &tmap, s << 7, (uint32_t)u0, mbar0 + 8u * buf);
     };
@@ -82,6 +84,9 @@ md5_strided_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uin
     // this thread's row, and the un-swizzle of its eight 16-byte chunks: chunk c sits at (c ^ (row & 7))
     const uint32_t rowoff = lane * 128u;
     const uint32_t swz = (lane & 7u) << 4;
+    uint32_t xo[8];                                           // byte offset of chunk c inside a stage buffer
+#pragma unroll
+    for (int c = 0; c < 8; ++c) xo[c] = rowoff + (((uint32_t)c << 4) ^ swz);
 
     // ---- whole stages ---------------------------------------------------------------------------
 #pragma unroll 1
@@ -89,15 +94,15 @@ md5_strided_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uin
         if (lane == 0 && s + (NSTAGE - 1) < nst) fetch(s + (NSTAGE - 1));
         const uint32_t buf = s % NSTAGE;
         mbar_wait(mbar0 + 8u * buf, (s / NSTAGE) & 1u);
-        const uint32_t row = wbase + buf * Cfg::STAGE_BYTES + rowoff;
-#pragma unroll 1
-        for (uint32_t j = 0; j < 2; ++j) {
+        const uint32_t tile = wbase + buf * Cfg::STAGE_BYTES;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
             uint32_t m[16];
 #pragma unroll
             for (int q = 0; q < 4; ++q)
                 asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
                              : "=r"(m[4 * q]), "=r"(m[4 * q + 1]), "=r"(m[4 * q + 2]), "=r"(m[4 * q + 3])
-                             : "r"(row + (((j * 4u + q) << 4) ^ swz)));
+                             : "r"(tile + xo[j * 4 + q]));
             md5_block<MODE>(st, m, one);
         }
         __syncwarp();                                         // all 32 rows consumed before the buffer is refilled

@@ -277,3 +277,92 @@ def test_tensor_map_kernel_for_strided_units(variant):
                 got = dig.cpu().numpy()
                 bad = np.nonzero((got != want).any(axis=1))[0]
                 assert bad.size == 0, (variant, stride, n, ragged, bad[:5])
+
+
+def _free_gib():
+    import torch
+    free, _ = torch.cuda.mem_get_info()
+    return free / (1 << 30)
+
+
+def test_full_size_properties_config3_s3_etag():
+    """BASELINE config 3, one of its 64 GiB files with 8 MiB parts, generated in HBM.  The oracle
+    cannot hash 64 GiB in seconds, so: a sample of part digests against the oracle, the
+    digest-of-digests against the oracle's MD5 of the GPU's own part digests (checks K2b and the
+    part count 8192), and the allocation-free/explicit-scratch variants agree."""
+    import torch
+    size, part = 64 << 30, 8 << 20
+    if _free_gib() < 70:
+        pytest.skip("needs 64 GiB of free HBM")
+    with tpi.Context([0]) as c:
+        d = torch.empty(size, dtype=torch.uint8, device="cuda")
+        c.dev_synth_fill(d, 3, 0, size, 1)                       # file 0 of workdir seed 3
+        n = tpi.s3_nparts(size, part)
+        assert n == 8192
+        parts = torch.zeros((n, 16), dtype=torch.uint8, device="cuda")
+        etag = torch.zeros(16, dtype=torch.uint8, device="cuda")
+        c.dev_s3_etag(d, size, part, etag, d_part_digests=parts)
+        torch.cuda.synchronize()
+        ph = parts.cpu().numpy()
+        for i in (0, 1, 4095, 8191):
+            assert ph[i].tobytes() == oracle.md5(oracle.synth_bytes(3, 0, part, i * part)), i
+        assert etag.cpu().numpy().tobytes() == oracle.md5(ph.tobytes())
+        etag2 = torch.zeros(16, dtype=torch.uint8, device="cuda")
+        c.dev_s3_etag(d, size, part, etag2)                      # library scratch
+        torch.cuda.synchronize()
+        assert torch.equal(etag, etag2)
+        # ragged: drop 5 bytes -> last part short, same part count; grow by one byte -> 8193 parts
+        c.dev_s3_etag(d, size - 5, part, etag2, d_part_digests=parts)
+        torch.cuda.synchronize()
+        ph2 = parts.cpu().numpy()
+        assert np.array_equal(ph2[:-1], ph[:-1]) and not np.array_equal(ph2[-1], ph[-1])
+        assert ph2[-1].tobytes() == oracle.md5(oracle.synth_bytes(3, 0, part - 5, 8191 * part))
+        assert etag2.cpu().numpy().tobytes() == oracle.md5(ph2.tobytes())
+
+
+def test_full_size_properties_config5_manifest_rebuild_and_diff():
+    """BASELINE config 5: 25,600 files x 4 MiB = 100 GiB, 1,280 files mutated by one byte (same size,
+    so only a checksum sees it).  Manifest rebuild + K4 diff must return exactly those 1,280 indices."""
+    import torch
+    n, flen = 25600, 4 << 20
+    if _free_gib() < 105:
+        pytest.skip("needs 100 GiB of free HBM")
+    with tpi.Context([0]) as c:
+        d = torch.empty(n * flen, dtype=torch.uint8, device="cuda")
+        c.dev_synth_fill(d, 5, 0, flen, n)
+        old = torch.zeros((n, 16), dtype=torch.uint8, device="cuda")
+        c.dev_hash_buffers(d, n * flen, n, old, stride=flen)
+        rng = np.random.default_rng(5)
+        victims = np.sort(rng.choice(n, 1280, replace=False))
+        offs = rng.integers(0, flen, 1280)
+        pos = torch.from_numpy(victims.astype(np.int64) * flen + offs).cuda()
+        d[pos] ^= 0x01
+        new = torch.zeros((n, 16), dtype=torch.uint8, device="cuda")
+        c.dev_hash_buffers(d, n * flen, n, new, stride=flen)
+        idx = torch.zeros(n, dtype=torch.int32, device="cuda")
+        cnt = torch.zeros(1, dtype=torch.int64, device="cuda")
+        c.dev_diff(old, new, n, idx, cnt)
+        torch.cuda.synchronize()
+        assert cnt.item() == 1280
+        assert np.array_equal(idx[:1280].cpu().numpy().astype(np.int64), victims)
+        oh = old.cpu().numpy()
+        for i in (0, 12345, n - 1):
+            assert oh[i].tobytes() == oracle.md5(oracle.synth_bytes(5, i, flen)), i
+        v = int(victims[7])
+        b = oracle.synth_bytes(5, v, flen).copy()
+        b[int(offs[7])] ^= 0x01
+        assert new[v].cpu().numpy().tobytes() == oracle.md5(b)
+
+
+def test_zipf_sizes_config4_shape_scaled():
+    """BASELINE config 4 scaled down (Zipf sizes 1 KiB .. 256 MiB, ~2 GiB): whole-file content-MD5 of a
+    skewed workdir through the host API; every digest against the oracle."""
+    k = np.arange(1, 4000)
+    sizes = np.maximum(1024, ((256 << 20) * k ** -1.111).astype(np.int64))
+    rng = np.random.default_rng(4)
+    rng.shuffle(sizes)
+    buf, off, ln = oracle.synth_packed(4, sizes.tolist(), align=1)
+    with tpi.Context([0], staging_bytes=64 << 20) as c:
+        got = c.hash_buffers(buf, off, ln)
+    want = oracle.md5_batch(buf, off, ln, threads=8, engine=oracle.ENGINE_OPENSSL if oracle.lib().orc_has_openssl() else 0)
+    assert np.array_equal(got, want)
