@@ -6,7 +6,7 @@ NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 OUT=terraform-provider-iterative_b200/libtpimd5.so
 $NVCC -std=c++17 -O3 -lineinfo -gencode arch=compute_100a,code=sm_100a \
       -Xcompiler -fPIC,-Wall,-Wextra,-fvisibility=hidden -Xptxas -v \
-      -shared -o "$OUT" csrc/tpimd5.cu -lpthread 2> build/ptxas.log || { cat build/ptxas.log; exit 1; }
+      -shared -o "$OUT" csrc/tpimd5.cu csrc/manifest.cc -lpthread 2> build/ptxas.log || { cat build/ptxas.log; exit 1; }
 grep -E "error|warning" build/ptxas.log | grep -v "ptxas info" || true
 make -s -C oracle
 echo "built $OUT"

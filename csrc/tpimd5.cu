@@ -57,6 +57,7 @@ static int fail(int code, const char *fmt, ...) {
     } while (0)
 
 extern "C" const char *tpimd5_last_error(void) { return g_err.c_str(); }
+extern "C" void tpimd5_set_error_(const char *msg) { g_err = msg ? msg : ""; }   // for the other translation units
 extern "C" const char *tpimd5_version(void) { return "tpimd5 0.1 (sm_100a)"; }
 
 // ------------------------------------------------------------------------------------------------

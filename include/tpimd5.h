@@ -101,6 +101,71 @@ TPIMD5_API void tpimd5_stream_close(tpimd5_stream *s);
 TPIMD5_API int tpimd5_diff(tpimd5_ctx *ctx, const uint8_t *old16, const uint8_t *new16, size_t n, uint32_t *changed_idx_out,
                 size_t *n_changed_out);
 
+/* ---- file set, manifest, transfer plan ---------------------------------------------------
+ * The host logic either side of the hash.
+ *
+ * tpimd5_filter_*: the set of files one machine.Transfer moves.  Reproduces the rule assembly of
+ * /root/reference/task/common/machine/storage.go:37-41,126-138 (built-in excludes "- /main.tf",
+ * "- /terraform.tfstate*", "- /.terraform**"; a rule without "+ "/"- " prefix becomes
+ * "- " + filepath.Join("/", rule)) and, when limit_subdir is non-NULL, LimitTransfer
+ * (storage.go:267-280: include that directory and everything beneath it, exclude the rest), with [rclone] fs/filter glob semantics
+ * (first matching rule wins, no match = include; a glob with a leading "/" matches from the root,
+ * any other glob after any "/"; "*" stays within a path segment, "**" does not).  Pinned by the
+ * expectations of storage_test.go:55-101.  Pure host code: works without a GPU.
+ *
+ * tpimd5_manifest_*: {relative path, size, mtime_ns, md5} per object, sorted by path.  The
+ * reference persists nothing (every sync re-lists and re-hashes); this is
+ * the persisted form the checkpoint loop of machine-script.sh.tpl:108-124 lacks.  _scan walks a
+ * local tree like [rclone] backend/local (regular files only, symlinks skipped), applies the
+ * filter and hashes every file on the GPU (tpimd5_hash_files).  _write_md5sum emits the
+ * "<32 hex>  <path>\n" lines of `md5sum` as used at machine-script.sh.tpl:111.
+ *
+ * tpimd5_plan_transfer: per source object, what [rclone] fs/march + fs/operations NeedTransfer/
+ * equal() decide for a copy src -> dst (sync.CopyDir, storage.go:158).  mode 0 = default
+ * (size, then modification-time window, then hash), 1 = --checksum, 2 = --size-only.  Digest
+ * comparisons run as one tpimd5_diff over all pairs that need one; ctx may be NULL only if none
+ * does.  actions_out: one TPIMD5_ACT_* per source entry, in manifest (path) order. */
+typedef struct tpimd5_filter tpimd5_filter;
+typedef struct tpimd5_manifest tpimd5_manifest;
+#define TPIMD5_ACT_SKIP          0   /* equal: nothing to do                                         */
+#define TPIMD5_ACT_TRANSFER_NEW  1   /* not at the destination                                       */
+#define TPIMD5_ACT_TRANSFER      2   /* present but different (size or digest)                       */
+#define TPIMD5_ACT_FIX_MTIME     3   /* same content, mtime outside the window: rclone updates mtime  */
+TPIMD5_API int tpimd5_filter_new(const char *const *exclude, size_t n_exclude, const char *limit_subdir, tpimd5_filter **out);
+TPIMD5_API void tpimd5_filter_free(tpimd5_filter *f);
+TPIMD5_API int tpimd5_filter_include(const tpimd5_filter *f, const char *rel_path);
+TPIMD5_API size_t tpimd5_filter_rule_count(const tpimd5_filter *f);
+TPIMD5_API const char *tpimd5_filter_rule(const tpimd5_filter *f, size_t i);
+TPIMD5_API int tpimd5_manifest_scan(tpimd5_ctx *ctx, const char *root, const tpimd5_filter *filter, tpimd5_manifest **out);
+TPIMD5_API int tpimd5_manifest_from_arrays(const char *const *paths, const uint64_t *sizes, const int64_t *mtimes_ns,
+                                           const uint8_t *md5s, const uint8_t *has_md5, size_t n, tpimd5_manifest **out);
+TPIMD5_API void tpimd5_manifest_free(tpimd5_manifest *m);
+TPIMD5_API size_t tpimd5_manifest_count(const tpimd5_manifest *m);
+TPIMD5_API int tpimd5_manifest_entry(const tpimd5_manifest *m, size_t i, const char **path, uint64_t *size, int64_t *mtime_ns,
+                                     uint8_t md5_out[16], int *has_md5);
+TPIMD5_API int tpimd5_manifest_save(const tpimd5_manifest *m, const char *file);
+TPIMD5_API int tpimd5_manifest_load(const char *file, tpimd5_manifest **out);
+TPIMD5_API int tpimd5_manifest_write_md5sum(const tpimd5_manifest *m, const char *file);
+TPIMD5_API int tpimd5_plan_transfer(tpimd5_ctx *ctx, const tpimd5_manifest *src, const tpimd5_manifest *dst, int mode,
+                                    int64_t window_ns, uint8_t *actions_out, size_t *n_transfer_out, size_t *n_dst_only_out);
+
+/* machine.Transfer(ctx, source, destination, exclude) for two LOCAL directories
+ * (/root/reference/task/common/machine/storage.go:123-159 -> sync.CopyDir(dst, src, true)): the
+ * case storage_test.go:55-101 runs and the tail of the Kubernetes Pull (task/k8s/task.go:294-299).
+ * Same filter on both sides, digests only where the mode consults them, equal() per object,
+ * directories created (also empty ones), modification times carried over, every copy verified by
+ * digest ("corrupted on transfer" removes the copy and fails).  All digests come from the GPU.
+ * Cloud remotes (":s3,...:bucket") remain rclone's job and are refused here.
+ * limit_subdir: NULL, or the DirectoryOut of a Pull (LimitTransfer).  mode as in plan_transfer. */
+typedef struct tpimd5_transfer_stats {
+    uint64_t files_listed, bytes_listed;        /* what operations.Count logs ("Transferring %s (%d files)...") */
+    uint64_t transferred, bytes_transferred;
+    uint64_t skipped, mtime_fixed, dst_only;
+    uint64_t bytes_hashed;                      /* bytes that went through the GPU (compare + verify) */
+} tpimd5_transfer_stats;
+TPIMD5_API int tpimd5_transfer_local(tpimd5_ctx *ctx, const char *source, const char *destination, const char *const *exclude,
+                                     size_t n_exclude, const char *limit_subdir, int mode, tpimd5_transfer_stats *stats_out);
+
 /* ---- device-resident variants ------------------------------------------------------------
  * Same arithmetic on data that already sits in HBM of the context's device `slot`; every
  * pointer is a device pointer and `cuda_stream` is a cudaStream_t (NULL = default stream).

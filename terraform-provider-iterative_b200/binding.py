@@ -22,7 +22,11 @@ EXPORTS = [
     "tpimd5_s3_etag_buffer", "tpimd5_s3_etag_file", "tpimd5_stream_open", "tpimd5_stream_write",
     "tpimd5_stream_write_many", "tpimd5_stream_sum", "tpimd5_stream_reset", "tpimd5_stream_close", "tpimd5_diff",
     "tpimd5_dev_hash_buffers", "tpimd5_dev_s3_etag", "tpimd5_dev_diff", "tpimd5_dev_synth_fill",
-    "tpimd5_dev_s3_etag_noalloc", "tpimd5_shard_lpt", "tpimd5_dev_int_probe", "tpimd5_launch_count", "tpimd5_set_variant",
+    "tpimd5_dev_s3_etag_noalloc", "tpimd5_filter_new", "tpimd5_filter_free", "tpimd5_filter_include",
+    "tpimd5_filter_rule_count", "tpimd5_filter_rule", "tpimd5_manifest_scan", "tpimd5_manifest_from_arrays",
+    "tpimd5_manifest_free", "tpimd5_manifest_count", "tpimd5_manifest_entry", "tpimd5_manifest_save",
+    "tpimd5_manifest_load", "tpimd5_manifest_write_md5sum", "tpimd5_plan_transfer", "tpimd5_transfer_local",
+    "tpimd5_shard_lpt", "tpimd5_dev_int_probe", "tpimd5_launch_count", "tpimd5_set_variant",
 ]
 
 
@@ -72,6 +76,22 @@ def load_library() -> C.CDLL:
         "tpimd5_dev_diff": (i32, [vp, i32, vp, vp, sz, vp, vp, vp]),
         "tpimd5_dev_synth_fill": (i32, [vp, i32, vp, u64, u64, u64, u64, vp]),
         "tpimd5_dev_s3_etag_noalloc": (i32, [i32, vp, u64, u64, vp, vp]),
+        "tpimd5_filter_new": (i32, [vp, sz, C.c_char_p, C.POINTER(vp)]),
+        "tpimd5_filter_free": (None, [vp]),
+        "tpimd5_filter_include": (i32, [vp, C.c_char_p]),
+        "tpimd5_filter_rule_count": (sz, [vp]),
+        "tpimd5_filter_rule": (C.c_char_p, [vp, sz]),
+        "tpimd5_manifest_scan": (i32, [vp, C.c_char_p, vp, C.POINTER(vp)]),
+        "tpimd5_manifest_from_arrays": (i32, [vp, vp, vp, vp, vp, sz, C.POINTER(vp)]),
+        "tpimd5_manifest_free": (None, [vp]),
+        "tpimd5_manifest_count": (sz, [vp]),
+        "tpimd5_manifest_entry": (i32, [vp, sz, C.POINTER(C.c_char_p), C.POINTER(u64), C.POINTER(C.c_int64), vp,
+                                        C.POINTER(i32)]),
+        "tpimd5_manifest_save": (i32, [vp, C.c_char_p]),
+        "tpimd5_manifest_load": (i32, [C.c_char_p, C.POINTER(vp)]),
+        "tpimd5_manifest_write_md5sum": (i32, [vp, C.c_char_p]),
+        "tpimd5_plan_transfer": (i32, [vp, vp, vp, i32, C.c_int64, vp, C.POINTER(sz), C.POINTER(sz)]),
+        "tpimd5_transfer_local": (i32, [vp, C.c_char_p, C.c_char_p, vp, sz, C.c_char_p, i32, vp]),
         "tpimd5_shard_lpt": (i32, [vp, sz, i32, vp]),
         "tpimd5_dev_int_probe": (i32, [vp, i32, i32, i32, u32, vp, C.POINTER(u64), vp]),
         "tpimd5_launch_count": (u64, [vp]),

@@ -1,0 +1,179 @@
+"""GPU tests of the callers either side of the hash: manifest scan, transfer plan, and
+machine.Transfer for local directories -- the latter written like the reference's own
+TestTransferExcludes (/root/reference/task/common/machine/storage_test.go:55-101)."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+import tpi_b200 as tpi
+from tpi_b200 import machine
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = tpi.Context([0], staging_bytes=16 << 20)
+    yield c
+    c.close()
+
+
+def list_dir(root):
+    """The reference test's listDir: every file and directory below root, as "/relative/path"."""
+    out = []
+    for d, dirs, files in os.walk(root):
+        for n in dirs + files:
+            out.append("/" + os.path.relpath(os.path.join(d, n), root).replace(os.sep, "/"))
+    return sorted(out)
+
+
+def make_transfer_test_tree(root):
+    """testdata/transferTest of the reference: four empty files."""
+    os.makedirs(os.path.join(root, "temp"))
+    for p in ("a.txt", "main.tf", "temp/a.txt", "temp/b.txt"):
+        open(os.path.join(root, p), "wb").close()
+
+
+@pytest.mark.parametrize("exclude,expect", [
+    (None, ["/a.txt", "/temp", "/temp/a.txt", "/temp/b.txt"]),           # built-in rules drop main.tf
+    (["**.txt"], ["/temp"]),                                             # directory still gets transferred
+    (["/a.txt"], ["/temp", "/temp/a.txt", "/temp/b.txt"]),               # explicitly anchored
+    (["a.txt"], ["/temp", "/temp/a.txt", "/temp/b.txt"]),                # implicitly anchored
+])
+def test_transfer_excludes(ctx, tmp_path, exclude, expect):
+    src, dst = str(tmp_path / "transferTest"), str(tmp_path / "dst")
+    make_transfer_test_tree(src)
+    machine.Transfer(ctx, src, dst, exclude)
+    assert list_dir(dst) == sorted(expect)
+
+
+def build_workdir(root, seed, n=60):
+    rng = np.random.default_rng(seed)
+    files = {}
+    for i in range(n):
+        d = ["", "data", "data/deep", "out", "cache", ".terraform/providers"][int(rng.integers(0, 6))]
+        name = f"f{i}" + [".bin", ".txt", ".ckpt"][int(rng.integers(0, 3))]
+        rel = (d + "/" if d else "") + name
+        size = int(rng.choice([0, 1, 55, 64, 4096, 70000, 3 << 20]))
+        os.makedirs(os.path.join(root, d), exist_ok=True)
+        b = oracle.synth_bytes(seed, i, size).tobytes()
+        with open(os.path.join(root, rel), "wb") as f:
+            f.write(b)
+        files[rel] = b
+    for rel in ("main.tf", "terraform.tfstate", "terraform.tfstate.backup"):
+        with open(os.path.join(root, rel), "wb") as f:
+            f.write(b"x")
+    os.symlink("main.tf", os.path.join(root, "link"))                       # rclone's local backend skips symlinks
+    return files
+
+
+def test_manifest_scan_is_the_filtered_listing_with_oracle_digests(ctx, tmp_path):
+    root = str(tmp_path / "w")
+    files = build_workdir(root, 61)
+    flt = tpi.Filter(["cache", "**.txt"])
+    m = tpi.Manifest.scan(ctx, root, flt)
+    o = oracle.FilterSet(oracle.transfer_rules(["cache", "**.txt"]))
+    want = sorted(p for p in files if o.include_file(p))
+    assert m.paths() == want and "link" not in m.paths()
+    for p, size, mtime, md5 in m.entries():
+        assert size == len(files[p]) and md5 == oracle.md5(files[p])
+        assert mtime == os.stat(os.path.join(root, p)).st_mtime_ns
+    out = str(tmp_path / "manifest.md5")
+    m.write_md5sum(out)
+    assert open(out).read() == "".join(oracle.md5sum_line(oracle.md5(files[p]), p) for p in want)
+    m.save(str(tmp_path / "m.tpim"))
+    assert tpi.Manifest.load(str(tmp_path / "m.tpim")).entries() == m.entries()
+
+
+def test_plan_transfer_follows_rclone_equal(ctx):
+    rng = np.random.default_rng(62)
+    n = 3000
+    paths = [f"d{i % 17}/f{i}" for i in range(n)]
+    sizes = rng.integers(0, 1000, n)
+    mt = rng.integers(0, 5, n)
+    md = rng.integers(0, 256, (n, 16), dtype=np.uint8)
+    have_s = rng.random(n) < 0.9
+    dsizes, dmt, dmd = sizes.copy(), mt.copy(), md.copy()
+    have_d = rng.random(n) < 0.9
+    for arr, frac in ((dsizes, 0.1), (dmt, 0.4)):
+        k = rng.random(n) < frac
+        arr[k] += 1
+    flip = rng.random(n) < 0.2
+    dmd[flip, 0] ^= 0xFF
+    present = rng.random(n) < 0.85
+    src = tpi.Manifest.from_arrays(paths, sizes, mt, md, have_s.astype(np.uint8))
+    keep = np.nonzero(present)[0]
+    dst = tpi.Manifest.from_arrays([paths[i] for i in keep] + ["zz/only-at-dst"], np.append(dsizes[keep], 5),
+                                   np.append(dmt[keep], 0), np.vstack([dmd[keep], np.zeros((1, 16), np.uint8)]),
+                                   np.append(have_d[keep], 1).astype(np.uint8))
+    order = {p: i for i, p in enumerate(paths)}
+    for mode in (tpi.manifest.MODE_MODTIME, tpi.manifest.MODE_CHECKSUM, tpi.manifest.MODE_SIZE_ONLY):
+        act, nt, nd = tpi.plan_transfer(ctx, src, dst, mode)
+        assert nd == 1
+        for (p, *_), a in zip(src.entries(), act.tolist()):
+            i = order[p]
+            if not present[i]:
+                assert a == tpi.manifest.ACT_TRANSFER_NEW
+                continue
+            eq, fix = oracle.equal(int(sizes[i]), int(dsizes[i]), int(mt[i]), int(dmt[i]),
+                                   md[i].tobytes() if have_s[i] else None, dmd[i].tobytes() if have_d[i] else None, mode=mode)
+            want = tpi.manifest.ACT_FIX_MTIME if (eq and fix) else (tpi.manifest.ACT_SKIP if eq else tpi.manifest.ACT_TRANSFER)
+            assert a == want, (mode, p)
+        assert nt == int(((act == 1) | (act == 2)).sum())
+
+
+def test_transfer_then_resync_with_checksum_finds_exactly_the_changed_files(ctx, tmp_path):
+    """BASELINE config 1 in miniature: sync a workdir to a local "remote", then mutate files without
+    touching size or mtime and resync with --checksum: only those move; a default-mode sync misses
+    them (as rclone's would), a resync after nothing changed moves nothing."""
+    src, dst = str(tmp_path / "src"), str(tmp_path / "dst")
+    files = build_workdir(src, 63, n=80)
+    st = machine.Transfer(ctx, src, dst, ["cache"])
+    o = oracle.FilterSet(oracle.transfer_rules(["cache"]))
+    moved = sorted(p for p in files if o.include_file(p))
+    assert st["transferred"] == len(moved) == st["files_listed"] and st["bytes_listed"] == sum(len(files[p]) for p in moved)
+    for p in moved:
+        assert open(os.path.join(dst, p), "rb").read() == files[p]
+        assert os.stat(os.path.join(dst, p)).st_mtime_ns == os.stat(os.path.join(src, p)).st_mtime_ns
+    # "cache" becomes "- /cache": that is a FILE named cache at the root (rclone glob semantics), so the
+    # directory cache/ still travels -- the oracle's filter agrees (it produced `moved`)
+    assert not os.path.exists(os.path.join(dst, "main.tf")) and not os.path.exists(os.path.join(dst, "terraform.tfstate"))
+    assert machine.Transfer(ctx, src, dst, ["cache"])["transferred"] == 0                      # unchanged: nothing moves
+    victims = [p for p in moved if len(files[p]) > 0][::7]
+    for p in victims:
+        full = os.path.join(src, p)
+        stt = os.stat(full)
+        b = bytearray(files[p]); b[len(b) // 2] ^= 1
+        with open(full, "wb") as f:
+            f.write(bytes(b))
+        os.utime(full, ns=(stt.st_atime_ns, stt.st_mtime_ns))                                   # same size, same mtime
+        files[p] = bytes(b)
+    assert machine.Transfer(ctx, src, dst, ["cache"])["transferred"] == 0                      # size+mtime cannot see it
+    st = machine.Transfer(ctx, src, dst, ["cache"], checksum=True)
+    assert st["transferred"] == len(victims) and st["skipped"] == len(moved) - len(victims)
+    for p in moved:
+        assert open(os.path.join(dst, p), "rb").read() == files[p]
+    # mtime-only change: default mode hashes the pair and fixes the destination mtime instead of copying
+    p = moved[0]
+    os.utime(os.path.join(src, p), ns=(1_000_000_000, 1_234_567_890_000_000_000))
+    st = machine.Transfer(ctx, src, dst, ["cache"])
+    assert st["transferred"] == 0 and st["mtime_fixed"] == 1
+    assert os.stat(os.path.join(dst, p)).st_mtime_ns == 1_234_567_890_000_000_000
+
+
+def test_pull_limited_to_the_output_directory(ctx, tmp_path):
+    """Pull: Transfer(remote/data, Directory, LimitTransfer(DirectoryOut, ExcludeList))
+    (/root/reference/task/aws/task.go:306-313): only out/ comes back, as the smoke test asserts."""
+    src, dst = str(tmp_path / "bucket-data"), str(tmp_path / "workdir")
+    files = build_workdir(src, 64, n=80)
+    machine.Transfer(ctx, src, dst, machine.LimitTransfer("out", ["cache"]))
+    got = [p[1:] for p in list_dir(dst) if os.path.isfile(os.path.join(dst, p[1:]))]
+    assert got == sorted(p for p in files if p.startswith("out/")) and got
+    assert not os.path.exists(os.path.join(dst, "cache")) and not os.path.exists(os.path.join(dst, "data"))
+
+
+def test_transfer_refuses_cloud_remotes(ctx, tmp_path):
+    with pytest.raises(tpi.TpiMd5Error):
+        machine.Transfer(ctx, str(tmp_path), ":s3,provider=AWS:bucket/data")
