@@ -55,7 +55,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--sweep", action="store_true", help="print kernel-only GB/s for every kernel variant, then exit")
-    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c5"],
+    ap.add_argument("--workload", default="c2", choices=["c1", "c2", "c3", "c5"],
                     help="c2 = the headline line (default); c3 = S3 ETag of 8 x 64 GiB files, 8 MiB parts (strong scaling); "
                          "c5 = 100 GiB manifest rebuild + diff.  c3/c5 print kernel-only lines for the record")
     return ap.parse_args()
@@ -218,6 +218,68 @@ def run_reference(args, rank, world):
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
+def run_c1(args, tpi, ctx):
+    """BASELINE config 1: 1,000 files / 1 GiB synced to a local-filesystem remote with --checksum.
+    Pass 1 copies, pass 2 (timed) finds nothing changed: both sides are hashed, 2 GiB through the GPU.
+    Beside it the same pass on the CPU, rclone-shaped (8 checkers x 2 sides, 32 KiB reads, OpenSSL MD5)."""
+    import shutil
+    import tempfile
+    import oracle
+    from tpi_b200 import machine
+    base = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else None
+    root = tempfile.mkdtemp(prefix="tpi_c1_", dir=base)
+    try:
+        rng = np.random.default_rng(1)
+        n = 1000
+        sizes = np.exp(rng.uniform(np.log(1 << 10), np.log(8 << 20), n))
+        sizes = np.maximum(1, (sizes * ((1 << 30) / sizes.sum())).astype(np.int64))
+        sizes[-1] += (1 << 30) - int(sizes.sum())
+        src, dst = os.path.join(root, "src"), os.path.join(root, "dst")
+        os.makedirs(src)
+        paths = []
+        for i, sz in enumerate(sizes.tolist()):
+            d = os.path.join(src, f"d{i % 16:02d}")
+            os.makedirs(d, exist_ok=True)
+            p = os.path.join(d, f"f{i:04d}.bin")
+            with open(p, "wb") as f:
+                f.write(oracle.synth_bytes(1, i, sz).tobytes())
+            paths.append(p)
+        t0 = time.perf_counter()
+        st1 = machine.Transfer(ctx, src, dst, None, checksum=True)
+        t_copy = time.perf_counter() - t0
+        assert st1["transferred"] == n
+        reps, t_gpu = max(3, args.e2e_steps), []
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            st2 = machine.Transfer(ctx, src, dst, None, checksum=True)
+            t_gpu.append(time.perf_counter() - t0)
+            assert st2["transferred"] == 0 and st2["skipped"] == n and st2["bytes_hashed"] == 2 << 30
+        both = paths + [p.replace(src, dst, 1) for p in paths]
+        eng = oracle.ENGINE_OPENSSL if oracle.lib().orc_has_openssl() else oracle.ENGINE_RESTATED
+        cpu = {}
+        for label, th in (("rclone_shape_16_threads", 16), ("all_cores", os.cpu_count() or 1)):
+            oracle.md5_files(both, threads=th, engine=eng)
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                oracle.md5_files(both, threads=th, engine=eng)
+            cpu[label] = round(reps * (2 << 30) / (time.perf_counter() - t0) / 1e9, 3)
+        best = min(t_gpu)
+        print(json.dumps({
+            "metric": METRIC, "value": round((2 << 30) / best / 1e9, 3), "unit": "GB/s", "n_gpus": 1, "steps": reps,
+            "warmup": 1, "ms_per_step": round(1e3 * best, 2), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u32", "data": "synthetic",
+            "config": {"workload": "C1: 1,000 files / 1 GiB, local->local sync with --checksum, unchanged second pass "
+                                   "(2 GiB hashed: both sides)", "where": root, "end_to_end": True,
+                       "first_pass_copy_verify_s": round(t_copy, 3)},
+            "cpu_baseline": {"value": cpu["rclone_shape_16_threads"], "unit": "GB/s", "cores": 16, "kind": "port",
+                             "sample": "the same 2,000 files read through 32 KiB buffers into OpenSSL MD5, one file per "
+                                       "thread, 16 threads (rclone: 8 checkers x 2 sides); all cores: "
+                                       f"{cpu['all_cores']} GB/s on {os.cpu_count()} threads"},
+            "gpu_launches": int(ctx.launch_count())}), flush=True)
+    finally:
+        shutil.rmtree(root, ignore_errors=True)
+
+
 def run_side_workload(args, torch, dist, tpi, ctx, dev, rank, world, barrier, max_over_ranks, stream):
     """Kernel-only lines for BASELINE configs 3 and 5 (not the headline; same JSON shape, fewer keys)."""
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -324,6 +386,12 @@ def main():
         ctx.set_variant(args.variant)
     stream = torch.cuda.current_stream().cuda_stream
 
+    if args.workload == "c1":
+        run_c1(args, tpi, ctx)
+        ctx.close()
+        if use_dist:
+            dist.destroy_process_group()
+        return 0
     if args.workload != "c2":
         run_side_workload(args, torch, dist, tpi, ctx, dev, rank, world, barrier, max_over_ranks, stream)
         ctx.close()

@@ -140,7 +140,7 @@ class Pool {
 // ------------------------------------------------------------------------------------------------
 // context
 // ------------------------------------------------------------------------------------------------
-constexpr int NBUF = 3;                       // staging buffers in flight per device
+constexpr int NBUF = 4;                       // staging buffers (and batch kernels) in flight per device
 constexpr size_t MAX_BATCH_LANES = 1u << 20;  // descriptor rows per staging buffer
 constexpr size_t DEFAULT_STAGING = 256u << 20;
 constexpr uint64_t MAX_LANE_BYTES = (uint64_t)60 << 30;  // one unit's bytes per launch (32-bit granule count)
@@ -154,6 +154,8 @@ struct Slot {
     int dev = -1;
     std::mutex mu;  // one call at a time per device
     cudaStream_t s_copy = nullptr, s_comp = nullptr;
+    cudaStream_t s_batch[NBUF] = {};  // one per staging buffer: kernels of successive batches overlap, which is
+                                      // what keeps many chains in flight when single units take tens of ms
     // ingest staging (allocated on first use)
     size_t stage_bytes = 0;
     bool staged = false;
@@ -260,6 +262,7 @@ extern "C" int tpimd5_init(const int *device_ids, int n_devices, size_t staging_
         CU(cudaSetDevice(dev));
         CU(cudaStreamCreateWithFlags(&s->s_copy, cudaStreamNonBlocking));
         CU(cudaStreamCreateWithFlags(&s->s_comp, cudaStreamNonBlocking));
+        for (int b = 0; b < NBUF; ++b) CU(cudaStreamCreateWithFlags(&s->s_batch[b], cudaStreamNonBlocking));
         ctx->slots.push_back(std::move(s));
     }
     unsigned hc = std::thread::hardware_concurrency();
@@ -275,6 +278,8 @@ extern "C" void tpimd5_destroy(tpimd5_ctx *ctx) {
         Slot &s = *sp;
         cudaSetDevice(s.dev);
         if (s.s_comp) cudaStreamSynchronize(s.s_comp);
+        for (int b = 0; b < NBUF; ++b)
+            if (s.s_batch[b]) { cudaStreamSynchronize(s.s_batch[b]); cudaStreamDestroy(s.s_batch[b]); }
         if (s.s_copy) cudaStreamSynchronize(s.s_copy);
         for (int i = 0; i < NBUF; ++i) {
             if (s.h_stage[i]) cudaFreeHost(s.h_stage[i]);
@@ -698,8 +703,16 @@ static int read_fully(int fd, uint8_t *dst, uint64_t off, uint64_t n) {
 }
 
 // Runs one device's share of a job.  `units` are indices into the job.
-static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint32_t> &units) {
-    if (units.empty()) return 0;
+static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint32_t> &units_in) {
+    if (units_in.empty()) return 0;
+    // Files: longest first.  One file is one serial chain (~125 MB/s), so the device's finish time is
+    // bounded by its longest file; starting those in the first batch lets the short ones fill in behind.
+    std::vector<uint32_t> by_size;
+    if (job.paths) {
+        by_size = units_in;
+        std::stable_sort(by_size.begin(), by_size.end(), [&](uint32_t a, uint32_t b) { return job.len[a] > job.len[b]; });
+    }
+    const std::vector<uint32_t> &units = job.paths ? by_size : units_in;
     std::lock_guard<std::mutex> guard(s.mu);
     CU(cudaSetDevice(s.dev));
     int rc = ensure_staging(ctx, s);
@@ -712,7 +725,7 @@ static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint
     // chaining values to start from
     if (job.init_states) {
         for (size_t i = 0; i < nu; ++i) memcpy(s.h_table + 16 * i, job.init_states + 16 * (size_t)units[i], 16);
-        CU(cudaMemcpyAsync(s.d_table, s.h_table, nu * 16, cudaMemcpyHostToDevice, s.s_comp));
+        CU(cudaMemcpyAsync(s.d_table, s.h_table, nu * 16, cudaMemcpyHostToDevice, s.s_copy));   // before any batch's data
     }
 
     // Direct mode: units already lie close together and in order in caller memory, so each batch is
@@ -847,21 +860,24 @@ static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint
         CU(cudaEventRecord(s.ev_copied[bi], s.s_copy));
 
         // ---- hash ------------------------------------------------------------------------------
-        CU(cudaStreamWaitEvent(s.s_comp, s.ev_copied[bi], 0));
+        cudaStream_t sk = s.s_batch[bi];
+        CU(cudaStreamWaitEvent(sk, s.ev_copied[bi], 0));
+        // a unit continued from the previous batch reads the chaining value that batch's kernel writes
+        if (batch > 0 && np && pieces[0].src_off > 0) CU(cudaStreamWaitEvent(sk, s.ev_done[(batch - 1) % NBUF], 0));
         LaneArgs a{};
         a.base = s.d_stage[bi]; a.base_bytes = used;
         a.off = s.dd[bi].off; a.len = s.dd[bi].len; a.prior = s.dd[bi].prior;
         a.flags = s.dd[bi].flags; a.out_idx = s.dd[bi].oidx;
         a.table = s.d_table; a.n = np;
-        rc = launch_lanes(ctx, a, aligned, s.s_comp);
+        rc = launch_lanes(ctx, a, aligned, sk);
         if (rc) return rc;
-        CU(cudaEventRecord(s.ev_done[bi], s.s_comp));
+        CU(cudaEventRecord(s.ev_done[bi], sk));
         ++batch;
     }
 
     if (io_err.load() != 0) {
         cudaStreamSynchronize(s.s_copy);
-        cudaStreamSynchronize(s.s_comp);
+        for (int b = 0; b < NBUF; ++b) cudaStreamSynchronize(s.s_batch[b]);
         const size_t u = io_idx.load();
         job.failed_index = u;
         const int e = io_err.load();
@@ -871,8 +887,9 @@ static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint
     }
 
     // ---- digests home -------------------------------------------------------------------------
-    CU(cudaMemcpyAsync(s.h_table, s.d_table, nu * 16, cudaMemcpyDeviceToHost, s.s_comp));
-    CU(cudaStreamSynchronize(s.s_comp));
+    for (int b = 0; b < NBUF && b < batch; ++b) CU(cudaStreamWaitEvent(s.s_copy, s.ev_done[b], 0));
+    CU(cudaMemcpyAsync(s.h_table, s.d_table, nu * 16, cudaMemcpyDeviceToHost, s.s_copy));
+    CU(cudaStreamSynchronize(s.s_copy));
     for (size_t i = 0; i < nu; ++i) memcpy(job.out + 16 * (size_t)units[i], s.h_table + 16 * i, 16);
     return 0;
 }

@@ -66,6 +66,8 @@ def lib() -> C.CDLL:
         L.orc_synth_fill.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint64]
         L.orc_synth_fill.restype = None
         L.orc_has_openssl.restype = C.c_int
+        L.orc_md5_files.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int]
+        L.orc_md5_files.restype = C.c_int
         _lib = L
     return _lib
 
@@ -133,6 +135,16 @@ def md5_batch(base, offsets, lengths, threads: int = 1, engine: int = ENGINE_RES
     if engine == ENGINE_OPENSSL and not lib().orc_has_openssl():
         raise RuntimeError("oracle built without OpenSSL")
     lib().orc_md5_batch(engine, a.ctypes.data, off.ctypes.data, ln.ctypes.data, off.size, out.ctypes.data, threads)
+    return out
+
+
+def md5_files(paths, threads: int = 1, engine: int = ENGINE_RESTATED) -> np.ndarray:
+    """rclone-shaped file hashing: one file per worker, 32 KiB reads -> uint8[n,16]."""
+    n = len(paths)
+    arr = (C.c_char_p * max(1, n))(*[os.fsencode(p) for p in paths])
+    out = np.zeros((n, 16), dtype=np.uint8)
+    if lib().orc_md5_files(engine, C.cast(arr, C.c_void_p), n, out.ctypes.data, threads) != 0:
+        raise OSError("orc_md5_files: a file could not be read")
     return out
 
 

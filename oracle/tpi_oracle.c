@@ -334,3 +334,82 @@ void orc_synth_fill(uint64_t seed, uint64_t file_index, uint64_t byte_offset, ui
         while (sh < 8 && pos < end) { *out++ = (uint8_t)(w >> (8 * sh)); sh++; pos++; }
     }
 }
+
+/* ------------------------------------------------------------------------------------------
+ * Files, the way rclone's local backend hashes them: open, io.Copy through a 32 KiB buffer into
+ * the hasher, close -- one file per worker at a time (rclone: 8 checkers, both sides of a pair
+ * concurrently).  Timing baseline for the file-ingest path; also a checker for tpimd5_hash_files.
+ * ---------------------------------------------------------------------------------------- */
+#include <fcntl.h>
+#include <unistd.h>
+
+typedef struct {
+    int engine;
+    const char *const *paths;
+    size_t n;
+    uint8_t *out;
+    int *errs;
+    size_t *next;
+    pthread_mutex_t *mu;
+} files_job;
+
+static int hash_one_file(int engine, const char *path, uint8_t out[16]) {
+    int fd = open(path, O_RDONLY);
+    if (fd < 0) return -1;
+    static __thread uint8_t buf[32768];
+    orc_md5_ctx c;
+#ifdef ORC_WITH_OPENSSL
+    MD5_CTX oc;
+    if (engine == 1) MD5_Init(&oc);
+#endif
+    orc_md5_init(&c);
+    for (;;) {
+        ssize_t k = read(fd, buf, sizeof buf);
+        if (k < 0) { close(fd); return -1; }
+        if (k == 0) break;
+#ifdef ORC_WITH_OPENSSL
+        if (engine == 1) { MD5_Update(&oc, buf, (size_t)k); continue; }
+#endif
+        orc_md5_update(&c, buf, (size_t)k);
+    }
+    close(fd);
+#ifdef ORC_WITH_OPENSSL
+    if (engine == 1) { MD5_Final(out, &oc); return 0; }
+#endif
+    orc_md5_sum(&c, out);
+    return 0;
+}
+
+static void *files_worker(void *arg) {
+    files_job *j = (files_job *)arg;
+    for (;;) {
+        pthread_mutex_lock(j->mu);
+        size_t i = (*j->next)++;
+        pthread_mutex_unlock(j->mu);
+        if (i >= j->n) break;
+        j->errs[i] = hash_one_file(j->engine, j->paths[i], j->out + 16 * i);
+    }
+    return NULL;
+}
+
+int orc_md5_files(int engine, const char *const *paths, size_t n, uint8_t *out, int nthreads) {
+    if (nthreads < 1) nthreads = 1;
+    if (nthreads > 256) nthreads = 256;
+    int *errs = (int *)calloc(n ? n : 1, sizeof(int));
+    if (!errs) return -2;
+    size_t next = 0;
+    pthread_mutex_t mu = PTHREAD_MUTEX_INITIALIZER;
+    files_job job = {engine, paths, n, out, errs, &next, &mu};
+    pthread_t th[256];
+    int started = 0;
+    for (int t = 0; t < nthreads; t++) {
+        if (pthread_create(&th[t], NULL, files_worker, &job) != 0) break;
+        started++;
+    }
+    if (!started) files_worker(&job);
+    for (int t = 0; t < started; t++) pthread_join(th[t], NULL);
+    int rc = 0;
+    for (size_t i = 0; i < n; i++) if (errs[i]) rc = -1;
+    free(errs);
+    return rc;
+}

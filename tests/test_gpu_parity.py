@@ -366,3 +366,43 @@ def test_zipf_sizes_config4_shape_scaled():
         got = c.hash_buffers(buf, off, ln)
     want = oracle.md5_batch(buf, off, ln, threads=8, engine=oracle.ENGINE_OPENSSL if oracle.lib().orc_has_openssl() else 0)
     assert np.array_equal(got, want)
+
+
+def test_one_context_many_threads(ctx):
+    """Terraform runs resource operations concurrently in one plugin process and rclone hashes from
+    8 checker + 4 transfer goroutines: a context must take calls from many threads at once."""
+    import threading
+    lengths = [int(x) for x in np.random.default_rng(71).integers(0, 50000, 300)]
+    buf, off, ln = oracle.synth_packed(71, lengths, align=1)
+    want = oracle.md5_batch(buf, off, ln, threads=4)
+    errs = []
+
+    def worker(k):
+        try:
+            for _ in range(3):
+                sel = np.arange(k, len(lengths), 4)
+                got = ctx.hash_buffers(buf, off[sel], ln[sel])
+                assert np.array_equal(got, want[sel])
+                assert ctx.diff(want, want).size == 0
+        except Exception as e:      # noqa: BLE001
+            errs.append(e)
+
+    th = [threading.Thread(target=worker, args=(k,)) for k in range(4)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errs, errs
+
+
+@pytest.mark.skipif(tpi.device_count() < 2, reason="needs two GPUs in one process")
+def test_one_context_two_devices_shards_and_gathers():
+    """In-process multi-GPU: units split byte-balanced over the context's devices, digests gathered
+    through pinned host memory; results must not depend on the split."""
+    rng = np.random.default_rng(72)
+    lengths = [int(x) for x in (rng.pareto(1.2, 3000) * 3000).astype(np.int64)] + [0, 40 << 20, 7]
+    buf, off, ln = oracle.synth_packed(72, lengths, align=16)
+    want = oracle.md5_batch(buf, off, ln, threads=8, engine=oracle.ENGINE_OPENSSL if oracle.lib().orc_has_openssl() else 0)
+    with tpi.Context(list(range(min(tpi.device_count(), 8))), staging_bytes=16 << 20) as c:
+        assert np.array_equal(c.hash_buffers(buf, off, ln), want)
+        etag, n, parts = c.s3_etag_buffer(buf[: 50 << 20], 1 << 20)
+        o = oracle.s3_etag(buf[: 50 << 20], 1 << 20, threads=4)
+        assert (etag, n) == (o[0], o[1]) and np.array_equal(parts, o[2])
