@@ -689,16 +689,22 @@ extern "C" int tpimd5_shard_lpt(const uint64_t *lengths, size_t n, int n_shards,
     return 0;
 }
 
-static int read_fully(int fd, uint8_t *dst, uint64_t off, uint64_t n) {
-    while (n) {
-        ssize_t r = pread(fd, dst, n > (1u << 30) ? (1u << 30) : (size_t)n, (off_t)off);
+// Reads exactly n bytes at `off`.  With `probe`, asks for one byte more: -3 if the file has it (it is
+// longer than listed), and end-of-file after exactly n bytes is the normal outcome.  -2: shorter.
+static int read_fully(int fd, uint8_t *dst, uint64_t off, uint64_t n, bool probe = false) {
+    uint64_t want = n + (probe ? 1 : 0), got = 0;
+    while (got < want) {
+        const uint64_t left = want - got;
+        ssize_t r = pread(fd, dst + got, left > (1u << 30) ? (1u << 30) : (size_t)left, (off_t)(off + got));
         if (r < 0) {
             if (errno == EINTR) continue;
             return -1;
         }
-        if (r == 0) return -2;  // shorter than promised
-        dst += r; off += (uint64_t)r; n -= (uint64_t)r;
+        if (r == 0) break;
+        got += (uint64_t)r;
     }
+    if (got < n) return -2;
+    if (got > n) return -3;
     return 0;
 }
 
@@ -775,9 +781,9 @@ static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint
             }
             if (dst > s.stage_bytes) break;
             const uint64_t space = s.stage_bytes - dst;
-            if (rem <= space) {
+            if (rem + (from_files ? 1 : 0) <= space) {
                 pieces.push_back({(uint32_t)ui, consumed, rem, dst, true});
-                used = dst + rem;
+                used = dst + rem + (from_files ? 1 : 0);      // files: one spare byte for the grew-since-listing probe
                 ++ui; consumed = 0;
             } else if (pieces.empty() || space >= (8u << 20)) {
                 const uint64_t take = space & ~(uint64_t)63;
@@ -825,16 +831,14 @@ static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint
             std::function<void(size_t)> fill = [&](size_t i) {
                 const Piece &p = pieces[i];
                 const uint32_t u = units[p.unit];
-                if (!p.len) return;
+                if (!p.len && !from_files) return;
                 if (from_files) {
                     int fd = open(job.paths[u], O_RDONLY | O_CLOEXEC);
                     const uint64_t fo = job.file_off ? job.file_off[u] : 0;
-                    int r = fd < 0 ? -1 : read_fully(fd, stage + p.dst, fo + p.src_off, p.len);
-                    if (fd >= 0 && p.last && r == 0 && !job.file_off) {
-                        // the listing promised exactly job.len[u] bytes: a longer file is a changed file
-                        uint8_t probe;
-                        if (pread(fd, &probe, 1, (off_t)(p.src_off + p.len)) > 0) r = -3;
-                    }
+                    // The listing promised exactly job.len[u] bytes.  Whole files are read with one byte
+                    // to spare (the packer leaves that byte free): getting it means the file grew.
+                    const bool probe = p.last && !job.file_off;
+                    int r = fd < 0 ? -1 : read_fully(fd, stage + p.dst, fo + p.src_off, p.len, probe);
                     if (fd >= 0) close(fd);
                     if (r != 0) {
                         int expect = 0;

@@ -118,6 +118,16 @@ def test_s3_etag_file_and_hash_files(ctx, tmp_path):
     with pytest.raises(tpi.TpiMd5Error) as e:
         ctx.hash_files(paths, [s + (1 if i == 2 else 0) for i, s in enumerate(sizes)])
     assert e.value.code == -4 and e.value.failed_index == 2
+    with pytest.raises(tpi.TpiMd5Error) as e:
+        ctx.hash_files(paths, [s - (1 if i == 3 else 0) for i, s in enumerate(sizes)])          # listed shorter than it is
+    assert e.value.code == -4 and e.value.failed_index == 3
+    with pytest.raises(tpi.TpiMd5Error) as e:
+        ctx.hash_files(paths, [1 if i == 0 else s for i, s in enumerate(sizes)])                # empty file listed as 1 byte
+    assert e.value.failed_index == 0
+    open(paths[0], "wb").write(b"x")                                                            # listed empty, has grown
+    with pytest.raises(tpi.TpiMd5Error) as e:
+        ctx.hash_files(paths, sizes)
+    assert e.value.failed_index == 0
     with pytest.raises(tpi.TpiMd5Error):
         ctx.hash_files(paths + [str(tmp_path / "missing")])
 
