@@ -492,6 +492,18 @@ def main():
             out = ctx.hash_buffers(host_np, off, ln)
         if not np.array_equal(out, digests.cpu().numpy()):
             raise SystemExit("bench.py: end-to-end digests differ from the kernel-only digests")
+        # ceiling of this leg: the same pinned buffer copied to the device and nothing else
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        scratch = torch.empty_like(data)
+        scratch.copy_(host, non_blocking=True)
+        torch.cuda.synchronize()
+        c0.record()
+        for _ in range(3):
+            scratch.copy_(host, non_blocking=True)
+        c1.record()
+        torch.cuda.synchronize()
+        h2d_gbps = 3 * nbytes / (c0.elapsed_time(c1) * 1e-3) / 1e9
+        del scratch
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.e2e_steps):
@@ -501,6 +513,8 @@ def main():
         e2e = {"value": round(world * nbytes * args.e2e_steps / dt / 1e9, 3), "unit": "GB/s",
                "h2d_bytes_per_step": int(nbytes + n * 32), "d2h_bytes_per_step": int(n * 16),
                "steps": args.e2e_steps, "ms_per_step": round(1e3 * dt / args.e2e_steps, 3),
+               "h2d_ceiling_GBps_per_gpu": round(h2d_gbps, 2),
+               "frac_of_h2d_ceiling": round(nbytes * args.e2e_steps / dt / 1e9 / h2d_gbps, 3),
                "api": "tpimd5_hash_buffers (host pointers, pinned source, H2D + kernel + D2H inside the timed region)"}
 
     # ---- CPU baseline beside it (rank 0, N=1 only) ------------------------------------------------

@@ -733,3 +733,56 @@ extern "C" int tpimd5_transfer_local(tpimd5_ctx *ctx, const char *source, const 
     if (stats_out) *stats_out = st;
     return 0;
 }
+
+// ------------------------------------------------------------------------------------------------
+// string forms of a digest that the S3 / Azure / GCS back-ends exchange
+// ------------------------------------------------------------------------------------------------
+// [rclone v1.57.0] backend/s3: Content-MD5 and the Md5chksum metadata are base64 of the 16 bytes;
+// Object.Hash accepts the ETag as an MD5 only if it is exactly 32 lowercase hex digits (multipart
+// "-N" and SSE-KMS ETags are not), see SURVEY.md appendix C.  azureblob Content-MD5 and GCS md5Hash
+// are base64 too; rclone's hash strings are lowercase hex.
+extern "C" void tpimd5_hex(const uint8_t md5[16], char out33[33]) {
+    static const char *hx = "0123456789abcdef";
+    for (int i = 0; i < 16; ++i) { out33[2 * i] = hx[md5[i] >> 4]; out33[2 * i + 1] = hx[md5[i] & 15]; }
+    out33[32] = 0;
+}
+
+extern "C" void tpimd5_base64(const uint8_t md5[16], char out25[25]) {
+    static const char *b64 = "ABCDEFGHIJKLMNOPQRSTUVWXYZabcdefghijklmnopqrstuvwxyz0123456789+/";
+    int o = 0;
+    for (int i = 0; i < 15; i += 3) {
+        const uint32_t v = (md5[i] << 16) | (md5[i + 1] << 8) | md5[i + 2];
+        out25[o++] = b64[v >> 18]; out25[o++] = b64[(v >> 12) & 63]; out25[o++] = b64[(v >> 6) & 63]; out25[o++] = b64[v & 63];
+    }
+    const uint32_t v = md5[15] << 16;
+    out25[o++] = b64[v >> 18]; out25[o++] = b64[(v >> 12) & 63]; out25[o++] = '='; out25[o++] = '=';
+    out25[o] = 0;
+}
+
+// 1 and the digest if `etag` (quotes allowed, as S3 returns it) is a plain MD5; 0 if it is a multipart
+// or otherwise opaque ETag -- then rclone falls back to the Md5chksum metadata or reports no hash.
+extern "C" int tpimd5_md5_from_etag(const char *etag, uint8_t md5_out[16]) {
+    if (!etag) return 0;
+    std::string e(etag);
+    if (e.size() >= 2 && e.front() == '"' && e.back() == '"') e = e.substr(1, e.size() - 2);
+    if (e.size() != 32) return 0;
+    uint8_t d[16];
+    for (int i = 0; i < 32; ++i) {
+        const char c = e[i];
+        int v;
+        if (c >= '0' && c <= '9') v = c - '0';
+        else if (c >= 'a' && c <= 'f') v = c - 'a' + 10;
+        else return 0;                                   // uppercase is not accepted either (matchMd5 is [0-9a-f]{32})
+        if (i & 1) d[i >> 1] |= (uint8_t)v; else d[i >> 1] = (uint8_t)(v << 4);
+    }
+    if (md5_out) memcpy(md5_out, d, 16);
+    return 1;
+}
+
+// "<32 hex>-<nparts>": the multipart ETag rclone expects back from S3 after CompleteMultipartUpload
+extern "C" int tpimd5_s3_etag_text(const uint8_t etag_md5[16], uint32_t nparts, char *out, size_t out_len) {
+    char hex[33];
+    tpimd5_hex(etag_md5, hex);
+    const int k = snprintf(out, out_len, "%s-%u", hex, nparts);
+    return (k > 0 && (size_t)k < out_len) ? 0 : fail(TPIMD5_EINVAL, "s3_etag_text: buffer too small");
+}

@@ -81,6 +81,17 @@ TPIMD5_API int tpimd5_s3_etag_buffer(tpimd5_ctx *ctx, const uint8_t *data, uint6
 TPIMD5_API int tpimd5_s3_etag_file(tpimd5_ctx *ctx, const char *path, uint64_t size, uint64_t part_size,
                         uint8_t *part_digests_out, uint8_t etag_md5_out[16], uint32_t *nparts_out);
 
+/* ---- digest strings -----------------------------------------------------------------------
+ * The textual forms the back-ends exchange ([rclone] backend/s3, azureblob, googlecloudstorage;
+ * registered at storage.go:18-21): lowercase hex (rclone hash strings, plain S3 ETags), base64
+ * (Content-MD5 per part / per object, X-Amz-Meta-Md5chksum, Azure Content-MD5, GCS md5Hash), the
+ * multipart ETag "<hex>-<nparts>", and rclone's test whether an ETag is an MD5 at all
+ * (exactly 32 lowercase hex digits; returns 1 and the bytes, else 0). */
+TPIMD5_API void tpimd5_hex(const uint8_t md5[16], char out33[33]);
+TPIMD5_API void tpimd5_base64(const uint8_t md5[16], char out25[25]);
+TPIMD5_API int tpimd5_md5_from_etag(const char *etag, uint8_t md5_out[16]);
+TPIMD5_API int tpimd5_s3_etag_text(const uint8_t etag_md5[16], uint32_t nparts, char *out, size_t out_len);
+
 /* ---- streaming hasher --------------------------------------------------------------------
  * Go hash.Hash as crypto/md5 implements it: Write (any chunking, never fails for lack of
  * data), Sum (finalises a copy, the stream continues), Reset, Size()==16, BlockSize()==64.

@@ -21,6 +21,9 @@ from .binding import (  # noqa: F401
     device_count,
     lib_path,
     load_library,
+    md5_base64,
+    md5_from_etag,
+    md5_hex,
     s3_etag_text,
     s3_nparts,
     s3_part_size,

@@ -26,6 +26,7 @@ EXPORTS = [
     "tpimd5_filter_rule_count", "tpimd5_filter_rule", "tpimd5_manifest_scan", "tpimd5_manifest_from_arrays",
     "tpimd5_manifest_free", "tpimd5_manifest_count", "tpimd5_manifest_entry", "tpimd5_manifest_save",
     "tpimd5_manifest_load", "tpimd5_manifest_write_md5sum", "tpimd5_plan_transfer", "tpimd5_transfer_local",
+    "tpimd5_hex", "tpimd5_base64", "tpimd5_md5_from_etag", "tpimd5_s3_etag_text",
     "tpimd5_shard_lpt", "tpimd5_dev_int_probe", "tpimd5_launch_count", "tpimd5_set_variant",
 ]
 
@@ -92,6 +93,10 @@ def load_library() -> C.CDLL:
         "tpimd5_manifest_write_md5sum": (i32, [vp, C.c_char_p]),
         "tpimd5_plan_transfer": (i32, [vp, vp, vp, i32, C.c_int64, vp, C.POINTER(sz), C.POINTER(sz)]),
         "tpimd5_transfer_local": (i32, [vp, C.c_char_p, C.c_char_p, vp, sz, C.c_char_p, i32, vp]),
+        "tpimd5_hex": (None, [vp, vp]),
+        "tpimd5_base64": (None, [vp, vp]),
+        "tpimd5_md5_from_etag": (i32, [C.c_char_p, vp]),
+        "tpimd5_s3_etag_text": (i32, [vp, u32, vp, sz]),
         "tpimd5_shard_lpt": (i32, [vp, sz, i32, vp]),
         "tpimd5_dev_int_probe": (i32, [vp, i32, i32, i32, u32, vp, C.POINTER(u64), vp]),
         "tpimd5_launch_count": (u64, [vp]),
@@ -124,7 +129,31 @@ def s3_nparts(size: int, part_size: int) -> int:
 
 def s3_etag_text(etag_md5: bytes, nparts: int) -> str:
     """rclone's expected multipart ETag string: lowercase hex + "-" + part count."""
-    return f"{bytes(etag_md5).hex()}-{nparts}"
+    d = (C.c_uint8 * 16).from_buffer_copy(bytes(etag_md5))
+    out = C.create_string_buffer(64)
+    _check(load_library().tpimd5_s3_etag_text(d, nparts, out, 64))
+    return out.value.decode()
+
+
+def md5_hex(md5: bytes) -> str:
+    d = (C.c_uint8 * 16).from_buffer_copy(bytes(md5))
+    out = C.create_string_buffer(33)
+    load_library().tpimd5_hex(d, out)
+    return out.value.decode()
+
+
+def md5_base64(md5: bytes) -> str:
+    """Content-MD5 / Md5chksum / GCS md5Hash form of a digest."""
+    d = (C.c_uint8 * 16).from_buffer_copy(bytes(md5))
+    out = C.create_string_buffer(25)
+    load_library().tpimd5_base64(d, out)
+    return out.value.decode()
+
+
+def md5_from_etag(etag: str) -> Optional[bytes]:
+    """rclone's rule: an S3 ETag is an MD5 only if it is exactly 32 lowercase hex digits."""
+    d = (C.c_uint8 * 16)()
+    return bytes(d) if load_library().tpimd5_md5_from_etag(etag.encode(), d) == 1 else None
 
 
 def shard_lpt(lengths, n_shards: int) -> np.ndarray:

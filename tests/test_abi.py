@@ -68,3 +68,16 @@ def test_no_cpu_fallback_without_gpu():
     with pytest.raises(tpi.TpiMd5Error) as e:
         tpi.Context()
     assert "no CPU fallback" in str(e.value)
+
+
+def test_digest_string_forms():
+    import base64
+    import hashlib
+    for msg in (b"", b"abc", bytes(range(256))):
+        d = hashlib.md5(msg).digest()
+        assert tpi.md5_hex(d) == d.hex()
+        assert tpi.md5_base64(d) == base64.b64encode(d).decode()
+        assert tpi.md5_from_etag(d.hex()) == d and tpi.md5_from_etag('"' + d.hex() + '"') == d
+        assert tpi.md5_from_etag(d.hex().upper()) is None or d.hex().upper() == d.hex()
+        assert tpi.md5_from_etag(d.hex() + "-3") is None and tpi.md5_from_etag(d.hex()[:-1]) is None
+        assert tpi.s3_etag_text(d, 8192) == d.hex() + "-8192"

@@ -177,3 +177,36 @@ def test_pull_limited_to_the_output_directory(ctx, tmp_path):
 def test_transfer_refuses_cloud_remotes(ctx, tmp_path):
     with pytest.raises(tpi.TpiMd5Error):
         machine.Transfer(ctx, str(tmp_path), ":s3,provider=AWS:bucket/data")
+
+
+CLI = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "terraform-provider-iterative_b200", "tpimd5sum")
+
+
+@pytest.mark.skipif(not os.path.exists(CLI), reason="tpimd5sum not built")
+def test_cli_prints_what_md5sum_prints_and_detects_changes(tmp_path):
+    """The VM script's change detectors (machine-script.sh.tpl:111,119) answered from the GPU."""
+    import subprocess
+    root = str(tmp_path / "logs")
+    files = build_workdir(root, 65, n=40)
+    names = sorted(p for p in files if "/" not in p)                        # like `md5sum "$DIR"/*`
+    got = subprocess.run([CLI] + names, cwd=root, capture_output=True, text=True)
+    assert got.returncode == 0, got.stderr
+    assert got.stdout == subprocess.check_output(["md5sum"] + names, cwd=root, text=True)
+    man = str(tmp_path / "old.tpim")
+    out = subprocess.run([CLI, "--manifest", root, "-x", "**.txt", "-o", man], capture_output=True, text=True)
+    o = oracle.FilterSet(oracle.transfer_rules(["**.txt"]))
+    keep = sorted(p for p in files if o.include_file(p))
+    assert out.returncode == 0 and out.stdout == "".join(oracle.md5sum_line(oracle.md5(files[p]), p) for p in keep)
+    # nothing changed -> exit 0 and no lines
+    r = subprocess.run([CLI, "--changed", man, root, "-x", "**.txt"], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout == ""
+    # one byte flipped with size and mtime restored, one new file -> exactly those two, exit 1
+    victim = next(p for p in keep if len(files[p]) > 10)
+    full = os.path.join(root, victim)
+    st = os.stat(full)
+    b = bytearray(files[victim]); b[3] ^= 0x80
+    open(full, "wb").write(bytes(b))
+    os.utime(full, ns=(st.st_atime_ns, st.st_mtime_ns))
+    open(os.path.join(root, "zz_new.bin"), "wb").write(b"new")
+    r = subprocess.run([CLI, "--changed", man, root, "-x", "**.txt"], capture_output=True, text=True)
+    assert r.returncode == 1 and sorted(r.stdout.splitlines()) == sorted([f"* {victim}", "+ zz_new.bin"])
