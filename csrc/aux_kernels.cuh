@@ -125,4 +125,29 @@ __global__ void __launch_bounds__(256) synth_fill_kernel(uint4 *__restrict__ out
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Length bucketing for ragged device-resident units.  A warp runs until its longest unit is done,
+// so 32 units of mixed length waste lanes.  Units are therefore ordered by block count (longest
+// first: their chains bound the finish time) with a device radix sort; digests still land at the
+// caller's index through out_idx.  These two kernels produce the keys and apply the permutation.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) bucket_keys_kernel(const uint64_t *__restrict__ len, uint64_t n, uint32_t *__restrict__ keys,
+                                                           uint32_t *__restrict__ idx) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t blocks = len[i] >> 6;
+    keys[i] = ~(uint32_t)(blocks > 0xffffffffull ? 0xffffffffull : blocks);      // ascending sort = longest first
+    idx[i] = (uint32_t)i;
+}
+
+__global__ void __launch_bounds__(256) bucket_gather_kernel(const uint64_t *__restrict__ off, const uint64_t *__restrict__ len,
+                                                             const uint32_t *__restrict__ perm, uint64_t n,
+                                                             uint64_t *__restrict__ off_out, uint64_t *__restrict__ len_out) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t j = perm[i];
+    off_out[i] = off[j];
+    len_out[i] = len[j];
+}
+
 }  // namespace tpimd5

@@ -95,16 +95,22 @@ md5_strided_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uin
         const uint32_t buf = s % NSTAGE;
         mbar_wait(mbar0 + 8u * buf, (s / NSTAGE) & 1u);
         const uint32_t tile = wbase + buf * Cfg::STAGE_BYTES;
+        // All 128 bytes of the row are read up front (8 x LDS.128), so the shared-memory latency is paid
+        // once per stage instead of once per load -- it is exposed when few chains share a scheduler
+        // (S3 parts, large files), and costs only registers when many do.
+        uint32_t m0[16], m1[16];
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
-            uint32_t m[16];
+        for (int q = 0; q < 4; ++q)
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(m0[4 * q]), "=r"(m0[4 * q + 1]), "=r"(m0[4 * q + 2]), "=r"(m0[4 * q + 3])
+                         : "r"(tile + xo[q]));
 #pragma unroll
-            for (int q = 0; q < 4; ++q)
-                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
-                             : "=r"(m[4 * q]), "=r"(m[4 * q + 1]), "=r"(m[4 * q + 2]), "=r"(m[4 * q + 3])
-                             : "r"(tile + xo[j * 4 + q]));
-            md5_block<MODE>(st, m, one);
-        }
+        for (int q = 0; q < 4; ++q)
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(m1[4 * q]), "=r"(m1[4 * q + 1]), "=r"(m1[4 * q + 2]), "=r"(m1[4 * q + 3])
+                         : "r"(tile + xo[4 + q]));
+        md5_block<MODE>(st, m0, one);
+        md5_block<MODE>(st, m1, one);
         __syncwarp();                                         // all 32 rows consumed before the buffer is refilled
     }
 

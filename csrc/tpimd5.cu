@@ -28,6 +28,8 @@
 #include <unistd.h>
 #include <vector>
 
+#include <cub/device/device_radix_sort.cuh>
+
 #include "aux_kernels.cuh"
 #include "md5_lanes.cuh"
 #include "md5_strided_tma.cuh"
@@ -500,8 +502,34 @@ extern "C" int tpimd5_dev_hash_buffers(tpimd5_ctx *ctx, int slot, const void *d_
     a.base = (const uint8_t *)d_base; a.base_bytes = base_bytes;
     a.off = d_offsets; a.len = d_lengths; a.stride = stride;
     a.table = (uint4 *)d_digests_out; a.n = n;
-    if (!d_offsets) return launch_strided(ctx, d_base, base_bytes, stride, n, (uint4 *)d_digests_out, (cudaStream_t)cuda_stream);
-    return launch_lanes(ctx, a, aligned, (cudaStream_t)cuda_stream);
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    if (!d_offsets) return launch_strided(ctx, d_base, base_bytes, stride, n, (uint4 *)d_digests_out, st);
+    if (n < 4096 || n > 0xffffffffull) return launch_lanes(ctx, a, aligned, st);
+    // Many units of arbitrary length: bucket them by block count first (aux_kernels.cuh) so that a
+    // warp's 32 units end together.  All temporaries live in the slot's scratch.
+    size_t cub_bytes = 0;
+    CU(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, (const uint32_t *)nullptr, (uint32_t *)nullptr, (const uint32_t *)nullptr,
+                                       (uint32_t *)nullptr, (int)n, 0, 32, st));
+    const size_t n4 = (n * 4 + 255) & ~(size_t)255, n8 = (n * 8 + 255) & ~(size_t)255;
+    uint8_t *base_scratch;
+    {
+        std::lock_guard<std::mutex> g(s->mu);      // the scratch is shared by calls on this slot
+        int rc = ensure_scratch(*s, 4 * n4 + 2 * n8 + cub_bytes + 256);
+        if (rc) return rc;
+        base_scratch = s->d_scratch;
+    }
+    uint32_t *keys_in = (uint32_t *)base_scratch, *keys_out = (uint32_t *)(base_scratch + n4);
+    uint32_t *idx_in = (uint32_t *)(base_scratch + 2 * n4), *perm = (uint32_t *)(base_scratch + 3 * n4);
+    uint64_t *off_s = (uint64_t *)(base_scratch + 4 * n4), *len_s = (uint64_t *)(base_scratch + 4 * n4 + n8);
+    void *cub_tmp = base_scratch + 4 * n4 + 2 * n8;
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    bucket_keys_kernel<<<grid, 256, 0, st>>>(d_lengths, n, keys_in, idx_in);
+    CU(cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, keys_in, keys_out, idx_in, perm, (int)n, 0, 32, st));
+    bucket_gather_kernel<<<grid, 256, 0, st>>>(d_offsets, d_lengths, perm, n, off_s, len_s);
+    CU(cudaGetLastError());
+    ctx->launches.fetch_add(3);
+    a.off = off_s; a.len = len_s; a.out_idx = perm;
+    return launch_lanes(ctx, a, aligned, st);
 }
 
 extern "C" uint64_t tpimd5_s3_part_size(uint64_t size, uint64_t chunk_size, uint32_t max_parts) {

@@ -416,3 +416,48 @@ def test_one_context_two_devices_shards_and_gathers():
         etag, n, parts = c.s3_etag_buffer(buf[: 50 << 20], 1 << 20)
         o = oracle.s3_etag(buf[: 50 << 20], 1 << 20, threads=4)
         assert (etag, n) == (o[0], o[1]) and np.array_equal(parts, o[2])
+
+
+def test_device_ragged_units_are_bucketed_by_length():
+    """Device-resident units of arbitrary length and alignment (>= 4096 of them take the radix-sort
+    bucketing path): digests must land at the caller's indices."""
+    import torch
+    rng = np.random.default_rng(73)
+    n = 30000
+    lengths = np.concatenate([rng.integers(0, 9000, n - 3), [0, 1 << 20, 63]]).astype(np.int64)
+    rng.shuffle(lengths)
+    buf, off, ln = oracle.synth_packed(73, lengths.tolist(), align=1)
+    want = oracle.md5_batch(buf, off, ln, threads=8, engine=oracle.ENGINE_OPENSSL if oracle.lib().orc_has_openssl() else 0)
+    with tpi.Context([0]) as c:
+        d = torch.from_numpy(buf).cuda()
+        d_off = torch.from_numpy(off.astype(np.int64)).cuda()
+        d_len = torch.from_numpy(ln.astype(np.int64)).cuda()
+        dig = torch.zeros((n, 16), dtype=torch.uint8, device="cuda")
+        for _ in range(2):                                           # twice: the scratch is reused
+            dig.zero_()
+            c.dev_hash_buffers(d, buf.size, n, dig, d_offsets=d_off, d_lengths=d_len)
+            torch.cuda.synchronize()
+            assert np.array_equal(dig.cpu().numpy(), want)
+
+
+def test_repeated_launches_are_deterministic():
+    """compute-sanitizer is closed on this pool, so shared-memory races are hunted the blunt way: the
+    same launch 30 times over, every kernel family, all digests identical every time."""
+    import torch
+    with tpi.Context([0]) as c:
+        n, flen = 40000, 4096 + 48
+        d = torch.empty(n * flen, dtype=torch.uint8, device="cuda")
+        c.dev_synth_fill(d, 74, 0, 16, n * flen // 16)
+        ref_s = torch.zeros((n, 16), dtype=torch.uint8, device="cuda")
+        c.dev_hash_buffers(d, n * flen, n, ref_s, stride=flen)                      # tensor-map kernel
+        off = torch.arange(n, dtype=torch.int64, device="cuda") * flen + 3          # general kernel, unaligned
+        ln = torch.full((n,), flen - 7, dtype=torch.int64, device="cuda")
+        ref_g = torch.zeros((n, 16), dtype=torch.uint8, device="cuda")
+        c.dev_hash_buffers(d, n * flen, n, ref_g, d_offsets=off, d_lengths=ln)
+        torch.cuda.synchronize()
+        out = torch.zeros((n, 16), dtype=torch.uint8, device="cuda")
+        for _ in range(30):
+            c.dev_hash_buffers(d, n * flen, n, out, stride=flen)
+            assert torch.equal(out, ref_s)
+            c.dev_hash_buffers(d, n * flen, n, out, d_offsets=off, d_lengths=ln)
+            assert torch.equal(out, ref_g)
