@@ -408,7 +408,7 @@ def main():
         ctx.dev_hash_buffers(data, nbytes, n, digests, stride=flen, stream=stream)
 
     if args.sweep:
-        for variant in [0, 4, 44, 202, 242, 244, 0]:
+        for variant in [0, 4, 44, 64, 202, 242, 262, 0]:
             ctx.set_variant(variant)
             for _ in range(3):
                 step()

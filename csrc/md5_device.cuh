@@ -46,7 +46,13 @@ __device__ __forceinline__ uint32_t mad1(uint32_t a, uint32_t one, uint32_t c) {
 
 //   MODE 4  like 1, but m+k as a plain add hidden from the optimiser (VIADD reg+imm: one register read)
 //   MODE 5  like 3, with the multiplier 1 read from the constant bank instead of a register
-//   MODE 6  steps alternate between 4 and 5
+//   MODE 6  steps alternate between 4 and 5 (every second step adds on the fma pipe)
+//   MODE 7  every third step on the fma pipe, MODE 8  two of three, MODE 9  one of four
+// fma_step<MODE>(i): does step i (0..63) of a mixed mode take the fma-pipe form?
+template <int MODE>
+__host__ __device__ constexpr int fma_step(int i) {
+    return MODE == 2 || MODE == 6 ? (i & 1) : MODE == 7 ? (i % 3 == 0) : MODE == 8 ? (i % 3 != 0) : MODE == 9 ? (i % 4 == 0) : 0;
+}
 __constant__ uint32_t c_one = 1u;
 
 __device__ __forceinline__ uint32_t add_imm(uint32_t a, uint32_t k) {
@@ -64,10 +70,10 @@ template <int MODE, int STEP_PARITY>
 __device__ __forceinline__ uint32_t step_sum(uint32_t a, uint32_t f, uint32_t m, uint32_t k, uint32_t one) {
     if (MODE == 0) {
         return (a + (m + k)) + f;
-    } else if (MODE == 4 || (MODE == 6 && STEP_PARITY == 0)) {
+    } else if (MODE == 4 || (MODE >= 6 && STEP_PARITY == 0)) {
         const uint32_t x = add_imm(m, k);
         return a + x + f;
-    } else if (MODE == 5 || MODE == 6) {
+    } else if (MODE >= 5) {
         const uint32_t x = add_imm(m, k);
         const uint32_t y = madc(a, x);
         return madc(f, y);
@@ -81,9 +87,9 @@ __device__ __forceinline__ uint32_t step_sum(uint32_t a, uint32_t f, uint32_t m,
     }
 }
 
-#define TPI_STEP(f, a, b, c, d, m, k, s)                                         \
+#define TPI_STEP(f, a, b, c, d, m, k, s, idx)                                    \
     {                                                                            \
-        const uint32_t t_ = step_sum<MODE, (s) & 1>((a), f((b), (c), (d)), (m), (uint32_t)(k), one); \
+        const uint32_t t_ = step_sum<MODE, fma_step<MODE>(idx)>((a), f((b), (c), (d)), (m), (uint32_t)(k), one); \
         (a) = (b) + rotl(t_, (s));                                               \
     }
 
@@ -92,73 +98,73 @@ template <int MODE>
 __device__ __forceinline__ void md5_block(uint32_t (&st)[4], const uint32_t (&m)[16], uint32_t one) {
     uint32_t a = st[0], b = st[1], c = st[2], d = st[3];
     // round 1: g = i
-    TPI_STEP(fF, a, b, c, d, m[0], 0xd76aa478u, 7)
-    TPI_STEP(fF, d, a, b, c, m[1], 0xe8c7b756u, 12)
-    TPI_STEP(fF, c, d, a, b, m[2], 0x242070dbu, 17)
-    TPI_STEP(fF, b, c, d, a, m[3], 0xc1bdceeeu, 22)
-    TPI_STEP(fF, a, b, c, d, m[4], 0xf57c0fafu, 7)
-    TPI_STEP(fF, d, a, b, c, m[5], 0x4787c62au, 12)
-    TPI_STEP(fF, c, d, a, b, m[6], 0xa8304613u, 17)
-    TPI_STEP(fF, b, c, d, a, m[7], 0xfd469501u, 22)
-    TPI_STEP(fF, a, b, c, d, m[8], 0x698098d8u, 7)
-    TPI_STEP(fF, d, a, b, c, m[9], 0x8b44f7afu, 12)
-    TPI_STEP(fF, c, d, a, b, m[10], 0xffff5bb1u, 17)
-    TPI_STEP(fF, b, c, d, a, m[11], 0x895cd7beu, 22)
-    TPI_STEP(fF, a, b, c, d, m[12], 0x6b901122u, 7)
-    TPI_STEP(fF, d, a, b, c, m[13], 0xfd987193u, 12)
-    TPI_STEP(fF, c, d, a, b, m[14], 0xa679438eu, 17)
-    TPI_STEP(fF, b, c, d, a, m[15], 0x49b40821u, 22)
+    TPI_STEP(fF, a, b, c, d, m[0], 0xd76aa478u, 7, 0)
+    TPI_STEP(fF, d, a, b, c, m[1], 0xe8c7b756u, 12, 1)
+    TPI_STEP(fF, c, d, a, b, m[2], 0x242070dbu, 17, 2)
+    TPI_STEP(fF, b, c, d, a, m[3], 0xc1bdceeeu, 22, 3)
+    TPI_STEP(fF, a, b, c, d, m[4], 0xf57c0fafu, 7, 4)
+    TPI_STEP(fF, d, a, b, c, m[5], 0x4787c62au, 12, 5)
+    TPI_STEP(fF, c, d, a, b, m[6], 0xa8304613u, 17, 6)
+    TPI_STEP(fF, b, c, d, a, m[7], 0xfd469501u, 22, 7)
+    TPI_STEP(fF, a, b, c, d, m[8], 0x698098d8u, 7, 8)
+    TPI_STEP(fF, d, a, b, c, m[9], 0x8b44f7afu, 12, 9)
+    TPI_STEP(fF, c, d, a, b, m[10], 0xffff5bb1u, 17, 10)
+    TPI_STEP(fF, b, c, d, a, m[11], 0x895cd7beu, 22, 11)
+    TPI_STEP(fF, a, b, c, d, m[12], 0x6b901122u, 7, 12)
+    TPI_STEP(fF, d, a, b, c, m[13], 0xfd987193u, 12, 13)
+    TPI_STEP(fF, c, d, a, b, m[14], 0xa679438eu, 17, 14)
+    TPI_STEP(fF, b, c, d, a, m[15], 0x49b40821u, 22, 15)
     // round 2: g = (5i + 1) mod 16
-    TPI_STEP(fG, a, b, c, d, m[1], 0xf61e2562u, 5)
-    TPI_STEP(fG, d, a, b, c, m[6], 0xc040b340u, 9)
-    TPI_STEP(fG, c, d, a, b, m[11], 0x265e5a51u, 14)
-    TPI_STEP(fG, b, c, d, a, m[0], 0xe9b6c7aau, 20)
-    TPI_STEP(fG, a, b, c, d, m[5], 0xd62f105du, 5)
-    TPI_STEP(fG, d, a, b, c, m[10], 0x02441453u, 9)
-    TPI_STEP(fG, c, d, a, b, m[15], 0xd8a1e681u, 14)
-    TPI_STEP(fG, b, c, d, a, m[4], 0xe7d3fbc8u, 20)
-    TPI_STEP(fG, a, b, c, d, m[9], 0x21e1cde6u, 5)
-    TPI_STEP(fG, d, a, b, c, m[14], 0xc33707d6u, 9)
-    TPI_STEP(fG, c, d, a, b, m[3], 0xf4d50d87u, 14)
-    TPI_STEP(fG, b, c, d, a, m[8], 0x455a14edu, 20)
-    TPI_STEP(fG, a, b, c, d, m[13], 0xa9e3e905u, 5)
-    TPI_STEP(fG, d, a, b, c, m[2], 0xfcefa3f8u, 9)
-    TPI_STEP(fG, c, d, a, b, m[7], 0x676f02d9u, 14)
-    TPI_STEP(fG, b, c, d, a, m[12], 0x8d2a4c8au, 20)
+    TPI_STEP(fG, a, b, c, d, m[1], 0xf61e2562u, 5, 16)
+    TPI_STEP(fG, d, a, b, c, m[6], 0xc040b340u, 9, 17)
+    TPI_STEP(fG, c, d, a, b, m[11], 0x265e5a51u, 14, 18)
+    TPI_STEP(fG, b, c, d, a, m[0], 0xe9b6c7aau, 20, 19)
+    TPI_STEP(fG, a, b, c, d, m[5], 0xd62f105du, 5, 20)
+    TPI_STEP(fG, d, a, b, c, m[10], 0x02441453u, 9, 21)
+    TPI_STEP(fG, c, d, a, b, m[15], 0xd8a1e681u, 14, 22)
+    TPI_STEP(fG, b, c, d, a, m[4], 0xe7d3fbc8u, 20, 23)
+    TPI_STEP(fG, a, b, c, d, m[9], 0x21e1cde6u, 5, 24)
+    TPI_STEP(fG, d, a, b, c, m[14], 0xc33707d6u, 9, 25)
+    TPI_STEP(fG, c, d, a, b, m[3], 0xf4d50d87u, 14, 26)
+    TPI_STEP(fG, b, c, d, a, m[8], 0x455a14edu, 20, 27)
+    TPI_STEP(fG, a, b, c, d, m[13], 0xa9e3e905u, 5, 28)
+    TPI_STEP(fG, d, a, b, c, m[2], 0xfcefa3f8u, 9, 29)
+    TPI_STEP(fG, c, d, a, b, m[7], 0x676f02d9u, 14, 30)
+    TPI_STEP(fG, b, c, d, a, m[12], 0x8d2a4c8au, 20, 31)
     // round 3: g = (3i + 5) mod 16
-    TPI_STEP(fH, a, b, c, d, m[5], 0xfffa3942u, 4)
-    TPI_STEP(fH, d, a, b, c, m[8], 0x8771f681u, 11)
-    TPI_STEP(fH, c, d, a, b, m[11], 0x6d9d6122u, 16)
-    TPI_STEP(fH, b, c, d, a, m[14], 0xfde5380cu, 23)
-    TPI_STEP(fH, a, b, c, d, m[1], 0xa4beea44u, 4)
-    TPI_STEP(fH, d, a, b, c, m[4], 0x4bdecfa9u, 11)
-    TPI_STEP(fH, c, d, a, b, m[7], 0xf6bb4b60u, 16)
-    TPI_STEP(fH, b, c, d, a, m[10], 0xbebfbc70u, 23)
-    TPI_STEP(fH, a, b, c, d, m[13], 0x289b7ec6u, 4)
-    TPI_STEP(fH, d, a, b, c, m[0], 0xeaa127fau, 11)
-    TPI_STEP(fH, c, d, a, b, m[3], 0xd4ef3085u, 16)
-    TPI_STEP(fH, b, c, d, a, m[6], 0x04881d05u, 23)
-    TPI_STEP(fH, a, b, c, d, m[9], 0xd9d4d039u, 4)
-    TPI_STEP(fH, d, a, b, c, m[12], 0xe6db99e5u, 11)
-    TPI_STEP(fH, c, d, a, b, m[15], 0x1fa27cf8u, 16)
-    TPI_STEP(fH, b, c, d, a, m[2], 0xc4ac5665u, 23)
+    TPI_STEP(fH, a, b, c, d, m[5], 0xfffa3942u, 4, 32)
+    TPI_STEP(fH, d, a, b, c, m[8], 0x8771f681u, 11, 33)
+    TPI_STEP(fH, c, d, a, b, m[11], 0x6d9d6122u, 16, 34)
+    TPI_STEP(fH, b, c, d, a, m[14], 0xfde5380cu, 23, 35)
+    TPI_STEP(fH, a, b, c, d, m[1], 0xa4beea44u, 4, 36)
+    TPI_STEP(fH, d, a, b, c, m[4], 0x4bdecfa9u, 11, 37)
+    TPI_STEP(fH, c, d, a, b, m[7], 0xf6bb4b60u, 16, 38)
+    TPI_STEP(fH, b, c, d, a, m[10], 0xbebfbc70u, 23, 39)
+    TPI_STEP(fH, a, b, c, d, m[13], 0x289b7ec6u, 4, 40)
+    TPI_STEP(fH, d, a, b, c, m[0], 0xeaa127fau, 11, 41)
+    TPI_STEP(fH, c, d, a, b, m[3], 0xd4ef3085u, 16, 42)
+    TPI_STEP(fH, b, c, d, a, m[6], 0x04881d05u, 23, 43)
+    TPI_STEP(fH, a, b, c, d, m[9], 0xd9d4d039u, 4, 44)
+    TPI_STEP(fH, d, a, b, c, m[12], 0xe6db99e5u, 11, 45)
+    TPI_STEP(fH, c, d, a, b, m[15], 0x1fa27cf8u, 16, 46)
+    TPI_STEP(fH, b, c, d, a, m[2], 0xc4ac5665u, 23, 47)
     // round 4: g = 7i mod 16
-    TPI_STEP(fI, a, b, c, d, m[0], 0xf4292244u, 6)
-    TPI_STEP(fI, d, a, b, c, m[7], 0x432aff97u, 10)
-    TPI_STEP(fI, c, d, a, b, m[14], 0xab9423a7u, 15)
-    TPI_STEP(fI, b, c, d, a, m[5], 0xfc93a039u, 21)
-    TPI_STEP(fI, a, b, c, d, m[12], 0x655b59c3u, 6)
-    TPI_STEP(fI, d, a, b, c, m[3], 0x8f0ccc92u, 10)
-    TPI_STEP(fI, c, d, a, b, m[10], 0xffeff47du, 15)
-    TPI_STEP(fI, b, c, d, a, m[1], 0x85845dd1u, 21)
-    TPI_STEP(fI, a, b, c, d, m[8], 0x6fa87e4fu, 6)
-    TPI_STEP(fI, d, a, b, c, m[15], 0xfe2ce6e0u, 10)
-    TPI_STEP(fI, c, d, a, b, m[6], 0xa3014314u, 15)
-    TPI_STEP(fI, b, c, d, a, m[13], 0x4e0811a1u, 21)
-    TPI_STEP(fI, a, b, c, d, m[4], 0xf7537e82u, 6)
-    TPI_STEP(fI, d, a, b, c, m[11], 0xbd3af235u, 10)
-    TPI_STEP(fI, c, d, a, b, m[2], 0x2ad7d2bbu, 15)
-    TPI_STEP(fI, b, c, d, a, m[9], 0xeb86d391u, 21)
+    TPI_STEP(fI, a, b, c, d, m[0], 0xf4292244u, 6, 48)
+    TPI_STEP(fI, d, a, b, c, m[7], 0x432aff97u, 10, 49)
+    TPI_STEP(fI, c, d, a, b, m[14], 0xab9423a7u, 15, 50)
+    TPI_STEP(fI, b, c, d, a, m[5], 0xfc93a039u, 21, 51)
+    TPI_STEP(fI, a, b, c, d, m[12], 0x655b59c3u, 6, 52)
+    TPI_STEP(fI, d, a, b, c, m[3], 0x8f0ccc92u, 10, 53)
+    TPI_STEP(fI, c, d, a, b, m[10], 0xffeff47du, 15, 54)
+    TPI_STEP(fI, b, c, d, a, m[1], 0x85845dd1u, 21, 55)
+    TPI_STEP(fI, a, b, c, d, m[8], 0x6fa87e4fu, 6, 56)
+    TPI_STEP(fI, d, a, b, c, m[15], 0xfe2ce6e0u, 10, 57)
+    TPI_STEP(fI, c, d, a, b, m[6], 0xa3014314u, 15, 58)
+    TPI_STEP(fI, b, c, d, a, m[13], 0x4e0811a1u, 21, 59)
+    TPI_STEP(fI, a, b, c, d, m[4], 0xf7537e82u, 6, 60)
+    TPI_STEP(fI, d, a, b, c, m[11], 0xbd3af235u, 10, 61)
+    TPI_STEP(fI, c, d, a, b, m[2], 0x2ad7d2bbu, 15, 62)
+    TPI_STEP(fI, b, c, d, a, m[9], 0xeb86d391u, 21, 63)
     st[0] += a; st[1] += b; st[2] += c; st[3] += d;
 }
 

@@ -411,6 +411,16 @@ static int launch_strided_tma(tpimd5_ctx *ctx, const void *base, uint64_t stride
     }
     if (mode == 0) {
         TPI_TMA(0)
+    } else if (mode == 5) {
+        TPI_TMA(5)
+    } else if (mode == 6) {
+        TPI_TMA(6)
+    } else if (mode == 7) {
+        TPI_TMA(7)
+    } else if (mode == 8) {
+        TPI_TMA(8)
+    } else if (mode == 9) {
+        TPI_TMA(9)
     } else {
         TPI_TMA(4)
     }
@@ -422,7 +432,7 @@ static int launch_strided_tma(tpimd5_ctx *ctx, const void *base, uint64_t stride
 // Kernel choice.  variant 0 = library default.  Otherwise 100*loader + 10*mode + shape, where loader
 // 0 forces the cp.async kernel everywhere and 2 allows the tensor-map kernel for strided units.
 static void decode_variant(int v, int &loader, int &mode, int &shape) {
-    if (v == 0) { loader = 2; mode = 4; shape = 0; return; }
+    if (v == 0) { loader = 2; mode = 6; shape = 0; return; }
     loader = v / 100; mode = (v / 10) % 10; shape = v % 10;
 }
 
@@ -437,14 +447,14 @@ static int launch_lanes(tpimd5_ctx *ctx, const LaneArgs &a0, bool aligned, cudaS
     if (aligned) {
         switch (mode) {
             case 0: rc = launch_variant<true, 0>(shape, a, st); break;
-            default: rc = launch_variant<true, 4>(shape, a, st); break;
-            case 6: rc = launch_variant<true, 6>(shape, a, st); break;
+            case 4: rc = launch_variant<true, 4>(shape, a, st); break;
+            default: rc = launch_variant<true, 6>(shape, a, st); break;
         }
     } else {
         switch (mode) {
             case 0: rc = launch_variant<false, 0>(shape, a, st); break;
-            default: rc = launch_variant<false, 4>(shape, a, st); break;
-            case 6: rc = launch_variant<false, 6>(shape, a, st); break;
+            case 4: rc = launch_variant<false, 4>(shape, a, st); break;
+            default: rc = launch_variant<false, 6>(shape, a, st); break;
         }
     }
     if (rc == 0) ctx->launches.fetch_add(1);
@@ -922,7 +932,13 @@ static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint
     for (int b = 0; b < NBUF && b < batch; ++b) CU(cudaStreamWaitEvent(s.s_copy, s.ev_done[b], 0));
     CU(cudaMemcpyAsync(s.h_table, s.d_table, nu * 16, cudaMemcpyDeviceToHost, s.s_copy));
     CU(cudaStreamSynchronize(s.s_copy));
-    for (size_t i = 0; i < nu; ++i) memcpy(job.out + 16 * (size_t)units[i], s.h_table + 16 * i, 16);
+    // table row i belongs to unit units[i]; runs of consecutive units move as one copy
+    for (size_t i = 0; i < nu;) {
+        size_t j = i + 1;
+        while (j < nu && units[j] == units[j - 1] + 1) ++j;
+        memcpy(job.out + 16 * (size_t)units[i], s.h_table + 16 * i, 16 * (j - i));
+        i = j;
+    }
     return 0;
 }
 

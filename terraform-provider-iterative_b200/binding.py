@@ -230,7 +230,7 @@ class Context:
         ln = np.ascontiguousarray(lengths, dtype=np.uint64)
         if off.shape != ln.shape or off.ndim != 1:
             raise ValueError("offsets and lengths must be 1-D and the same length")
-        out = np.zeros((off.size, 16), dtype=np.uint8)
+        out = np.empty((off.size, 16), dtype=np.uint8)
         if isinstance(base, int):
             bp = base
         else:

@@ -261,7 +261,7 @@ def test_full_size_properties_config2():
         assert cnt.item() == 1 and idx[0].item() == victim
 
 
-@pytest.mark.parametrize("variant", [0, 201, 202, 203, 204, 241, 244])
+@pytest.mark.parametrize("variant", [0, 201, 202, 203, 204, 241, 244, 262, 272, 282, 292])
 def test_tensor_map_kernel_for_strided_units(variant):
     """Equal-sized units at a fixed stride through the TMA kernel: every stride class (multiples of
     16 around the 64/128-byte block and stage boundaries), unit counts that do not fill the last
@@ -461,3 +461,16 @@ def test_repeated_launches_are_deterministic():
             assert torch.equal(out, ref_s)
             c.dev_hash_buffers(d, n * flen, n, out, d_offsets=off, d_lengths=ln)
             assert torch.equal(out, ref_g)
+
+
+def test_more_units_than_one_batch_of_descriptors(ctx):
+    """1.3 M tiny units: a batch closes at 1 Mi descriptor rows even though the staging buffer is nearly
+    empty, so this goes through several batches; plus empty units in bulk."""
+    n = 1_300_000
+    rng = np.random.default_rng(75)
+    ln = rng.integers(0, 9, n).astype(np.uint64)
+    off = np.concatenate([[0], np.cumsum(ln)[:-1]]).astype(np.uint64)
+    buf = oracle.synth_bytes(75, 0, int(ln.sum()) + 1)
+    got = ctx.hash_buffers(buf, off, ln)
+    want = oracle.md5_batch(buf, off, ln, threads=8, engine=oracle.ENGINE_OPENSSL if oracle.lib().orc_has_openssl() else 0)
+    assert np.array_equal(got, want)
