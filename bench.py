@@ -218,6 +218,25 @@ def run_reference(args, rank, world):
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
+def bind_near_gpu(index: int):
+    """Run this rank's host threads (and first-touch its pinned buffers) on the CPUs next to its GPU:
+    at 8 ranks the H2D copies otherwise cross the socket interconnect.  Best effort; returns the CPU list."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = [64 * w + b for w, mask in enumerate(words) for b in range(64) if (mask >> b) & 1 and 64 * w + b < ncpu]
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if len(allowed) >= 2:
+            os.sched_setaffinity(0, allowed)
+            return allowed
+    except Exception:
+        pass
+    return None
+
+
 def run_c1(args, tpi, ctx):
     """BASELINE config 1: 1,000 files / 1 GiB synced to a local-filesystem remote with --checksum.
     Pass 1 copies, pass 2 (timed) finds nothing changed: both sides are hashed, 2 GiB through the GPU.
@@ -360,6 +379,7 @@ def main():
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the checksum path has no CPU fallback (use --impl reference for the CPU arm)")
+    near = bind_near_gpu(local_rank) if world > 1 else None
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     use_dist = world > 1
@@ -492,11 +512,12 @@ def main():
             out = ctx.hash_buffers(host_np, off, ln)
         if not np.array_equal(out, digests.cpu().numpy()):
             raise SystemExit("bench.py: end-to-end digests differ from the kernel-only digests")
-        # ceiling of this leg: the same pinned buffer copied to the device and nothing else
+        # ceiling of this leg: the same pinned buffer copied to the device and nothing else (all ranks
+        # at once, as in the timed region: GPUs may share PCIe uplinks and the host's memory bandwidth)
         c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         scratch = torch.empty_like(data)
         scratch.copy_(host, non_blocking=True)
-        torch.cuda.synchronize()
+        barrier()
         c0.record()
         for _ in range(3):
             scratch.copy_(host, non_blocking=True)
@@ -513,7 +534,7 @@ def main():
         e2e = {"value": round(world * nbytes * args.e2e_steps / dt / 1e9, 3), "unit": "GB/s",
                "h2d_bytes_per_step": int(nbytes + n * 32), "d2h_bytes_per_step": int(n * 16),
                "steps": args.e2e_steps, "ms_per_step": round(1e3 * dt / args.e2e_steps, 3),
-               "h2d_ceiling_GBps_per_gpu": round(h2d_gbps, 2),
+               "h2d_ceiling_GBps_per_gpu": round(h2d_gbps, 2), "host_cpus_bound_near_gpu": (len(near) if near else None),
                "frac_of_h2d_ceiling": round(nbytes * args.e2e_steps / dt / 1e9 / h2d_gbps, 3),
                "api": "tpimd5_hash_buffers (host pointers, pinned source, H2D + kernel + D2H inside the timed region)"}
 
