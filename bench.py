@@ -55,7 +55,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--sweep", action="store_true", help="print kernel-only GB/s for every kernel variant, then exit")
-    ap.add_argument("--workload", default="c2", choices=["c1", "c2", "c3", "c5"],
+    ap.add_argument("--workload", default="c2", choices=["c1", "c2", "c3", "c4", "c5"],
                     help="c2 = the headline line (default); c3 = S3 ETag of 8 x 64 GiB files, 8 MiB parts (strong scaling); "
                          "c5 = 100 GiB manifest rebuild + diff.  c3/c5 print kernel-only lines for the record")
     return ap.parse_args()
@@ -303,7 +303,31 @@ def run_side_workload(args, torch, dist, tpi, ctx, dev, rank, world, barrier, ma
     """Kernel-only lines for BASELINE configs 3 and 5 (not the headline; same JSON shape, fewer keys)."""
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     peak = float(json.load(open(peaks_path))["hbm_gbs"]) if os.path.exists(peaks_path) else 6650.0
-    if args.workload == "c3":
+    if args.workload == "c4":
+        # BASELINE config 4 scaled by 1/64 so that it fits one GPU and a step takes seconds: rank-size Zipf
+        # floor(512 MiB * k^-1.111), smallest 1 KiB, whole-file content-MD5; files spread over the ranks by LPT
+        s_exp, top = 1.111, 512 << 20
+        nfiles = int(np.ceil((top / 1024) ** (1 / s_exp)))
+        k = np.arange(1, nfiles + 1, dtype=np.float64)
+        sizes = np.maximum(1024, np.floor(top * k ** (-s_exp))).astype(np.int64)
+        np.random.default_rng(4).shuffle(sizes)
+        assign = tpi.shard_lpt(sizes, world)
+        mine = sizes[assign == rank]
+        off = np.concatenate([[0], np.cumsum((mine + 15) // 16 * 16)[:-1]]).astype(np.int64)
+        total = int(off[-1] + mine[-1])
+        data = torch.empty((total + 15) // 16 * 16, dtype=torch.uint8, device=dev)
+        ctx.dev_synth_fill(data, 4, rank, 16, data.numel() // 16, stream=stream)
+        d_off, d_len = torch.from_numpy(off).to(dev), torch.from_numpy(mine).to(dev)
+        dig = torch.empty((mine.size, 16), dtype=torch.uint8, device=dev)
+
+        def step():
+            ctx.dev_hash_buffers(data, total, mine.size, dig, d_offsets=d_off, d_lengths=d_len, stream=stream)
+        work_bytes = int(sizes.sum())
+        label = (f"C4 scaled 1/64: {nfiles:,} files, Zipf 1 KiB..512 MiB ({work_bytes / 2**30:.1f} GiB), whole-file content-MD5, "
+                 f"byte-balanced LPT sharding; tail bound = largest file / single-chain rate = {top / 0.164e9:.1f} s at the "
+                 f"12-cycle/step floor")
+        scaling = "strong"
+    elif args.workload == "c3":
         size, part, files = 64 << 30, 8 << 20, 8
         mine = [f for f in range(files) if f % world == rank]
         data = torch.empty(size, dtype=torch.uint8, device=dev)
