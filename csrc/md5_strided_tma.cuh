@@ -30,19 +30,25 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *tma
         : "memory");
 }
 
-template <int WARPS, int NSTAGE>
+// TILES: boxes per stage.  1 keeps shared memory small (20 warps/SM for throughput-bound launches);
+// 2 or 4 halve / quarter the per-stage costs that sit on a lone chain's critical path (mbarrier wait,
+// TMA issue, loop) for launches with too few chains to fill the SMs (S3 parts, large files).
+template <int WARPS, int NSTAGE, int TILES = 1>
 struct StridedCfg {
-    static constexpr int STAGE_BYTES = 32 * 128;                    // one box
+    static constexpr int TILE_BYTES = 32 * 128;                     // one box
+    static constexpr int STAGE_BYTES = TILES * TILE_BYTES;
     static constexpr int WARP_BYTES = NSTAGE * STAGE_BYTES;
     static constexpr int DATA_BYTES = WARPS * WARP_BYTES;
     static constexpr int SMEM_BYTES = DATA_BYTES + WARPS * NSTAGE * 8 + 1024;   // + mbarriers + slack to align to 1 KiB
 };
 
-template <int WARPS, int MINB, int NSTAGE, int MODE>
+template <int WARPS, int MINB, int NSTAGE, int MODE, int TILES = 1>
 __global__ void __launch_bounds__(WARPS * 32, MINB)
 md5_strided_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uint32_t unit_len, uint4 *__restrict__ table,
                        uint32_t one) {
-    using Cfg = StridedCfg<WARPS, NSTAGE>;
+    using Cfg = StridedCfg<WARPS, NSTAGE, TILES>;
+    constexpr uint32_t SB = 128u * TILES;                     // bytes of one unit per stage
+    constexpr uint32_t BPS = 2u * TILES;                      // MD5 blocks per stage
     extern __shared__ uint8_t smem_raw[];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint64_t u0 = ((uint64_t)blockIdx.x * WARPS + warp) * 32u;         // first unit of this warp
@@ -60,8 +66,8 @@ md5_strided_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uin
     }
     __syncwarp();
 
-    const uint32_t nst = (unit_len + 127u) >> 7;              // stages that hold data
-    const uint32_t full_st = unit_len >> 7;                   // stages whose two blocks are both whole
+    const uint32_t nst = (unit_len + SB - 1u) / SB;           // stages that hold data
+    const uint32_t full_st = unit_len / SB;                   // stages whose blocks are all whole
     const uint32_t bm = unit_len >> 6;                        // block that takes the 0x80 marker
     const uint32_t nb = ((unit_len + 8u) >> 6) + 1u;          // blocks incl. padding
 
@@ -71,7 +77,10 @@ md5_strided_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uin
     auto fetch = [&](uint32_t s) {
         const uint32_t buf = s % NSTAGE;
         mbar_expect_tx(mbar0 + 8u * buf, Cfg::STAGE_BYTES);
-        tma_load_2d(wbase + buf * Cfg::STAGE_BYTES, &tmap, s << 7, (uint32_t)u0, mbar0 + 8u * buf);
+#pragma unroll
+        for (int t = 0; t < TILES; ++t)                       // a box wholly past unit_len arrives as zeros
+            tma_load_2d(wbase + buf * Cfg::STAGE_BYTES + t * Cfg::TILE_BYTES, &tmap, (s * TILES + t) << 7, (uint32_t)u0,
+                        mbar0 + 8u * buf);
     };
     if (lane == 0) {
 #pragma unroll
@@ -94,38 +103,41 @@ md5_strided_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uin
         if (lane == 0 && s + (NSTAGE - 1) < nst) fetch(s + (NSTAGE - 1));
         const uint32_t buf = s % NSTAGE;
         mbar_wait(mbar0 + 8u * buf, (s / NSTAGE) & 1u);
-        const uint32_t tile = wbase + buf * Cfg::STAGE_BYTES;
-        // All 128 bytes of the row are read up front (8 x LDS.128), so the shared-memory latency is paid
-        // once per stage instead of once per load -- it is exposed when few chains share a scheduler
+        // All 128 bytes of a row are read up front (8 x LDS.128), so the shared-memory latency is paid
+        // once per box instead of once per load -- it is exposed when few chains share a scheduler
         // (S3 parts, large files), and costs only registers when many do.
-        uint32_t m0[16], m1[16];
+        constexpr int GROUP = TILES >= 2 ? 2 : 1;             // boxes whose words are loaded before any is hashed
 #pragma unroll
-        for (int q = 0; q < 4; ++q)
-            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
-                         : "=r"(m0[4 * q]), "=r"(m0[4 * q + 1]), "=r"(m0[4 * q + 2]), "=r"(m0[4 * q + 3])
-                         : "r"(tile + xo[q]));
+        for (int t0 = 0; t0 < TILES; t0 += GROUP) {
+            uint32_t m[GROUP * 2][16];
 #pragma unroll
-        for (int q = 0; q < 4; ++q)
-            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
-                         : "=r"(m1[4 * q]), "=r"(m1[4 * q + 1]), "=r"(m1[4 * q + 2]), "=r"(m1[4 * q + 3])
-                         : "r"(tile + xo[4 + q]));
-        md5_block<MODE>(st, m0, one);
-        md5_block<MODE>(st, m1, one);
+            for (int g = 0; g < GROUP; ++g) {
+                const uint32_t tile = wbase + buf * Cfg::STAGE_BYTES + (t0 + g) * Cfg::TILE_BYTES;
+#pragma unroll
+                for (int q = 0; q < 8; ++q)
+                    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                                 : "=r"(m[2 * g + (q >> 2)][4 * (q & 3)]), "=r"(m[2 * g + (q >> 2)][4 * (q & 3) + 1]),
+                                   "=r"(m[2 * g + (q >> 2)][4 * (q & 3) + 2]), "=r"(m[2 * g + (q >> 2)][4 * (q & 3) + 3])
+                                 : "r"(tile + xo[q]));
+            }
+#pragma unroll
+            for (int k = 0; k < GROUP * 2; ++k) md5_block<MODE>(st, m[k], one);
+        }
         __syncwarp();                                         // all 32 rows consumed before the buffer is refilled
     }
 
-    // ---- tail: a partial stage (if unit_len is not a multiple of 128) and the padding ---------------
+    // ---- tail: a partial stage (if unit_len is not a multiple of the stage) and the padding -----------
 #pragma unroll 1
-    for (uint32_t b = full_st * 2u; b < nb; ++b) {
-        const uint32_t s = b >> 1, j = b & 1u;
+    for (uint32_t b = full_st * BPS; b < nb; ++b) {
+        const uint32_t s = b / BPS, within = b % BPS, j = within & 1u;
         const uint32_t buf = s % NSTAGE;
-        if (j == 0 && s < nst) {
+        if (within == 0 && s < nst) {
             if (lane == 0 && s + (NSTAGE - 1) < nst) fetch(s + (NSTAGE - 1));
             mbar_wait(mbar0 + 8u * buf, (s / NSTAGE) & 1u);
         }
         uint32_t m[16];
         if (b <= bm && s < nst) {
-            const uint32_t row = wbase + buf * Cfg::STAGE_BYTES + rowoff;
+            const uint32_t row = wbase + buf * Cfg::STAGE_BYTES + (within >> 1) * Cfg::TILE_BYTES + rowoff;
 #pragma unroll
             for (int q = 0; q < 4; ++q)
                 asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
@@ -137,7 +149,7 @@ md5_strided_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uin
         }
         if (b >= bm) md5_pad_block(m, unit_len & 63u, b > bm, (uint64_t)unit_len);
         md5_block<MODE>(st, m, one);
-        if (j == 1) __syncwarp();
+        if (within == BPS - 1) __syncwarp();
     }
     if (u < n) table[u] = make_uint4(st[0], st[1], st[2], st[3]);
 }

@@ -369,10 +369,10 @@ static bool tma_eligible(const void *base, uint64_t stride, uint64_t unit_len, u
            unit_len <= stride && unit_len <= ((uint64_t)1 << 31) && n >= 1 && n <= ((uint64_t)1 << 31) && encode_tiled_fn() != nullptr;
 }
 
-template <int WARPS, int MINB, int NSTAGE, int MODE>
+template <int WARPS, int MINB, int NSTAGE, int MODE, int TILES = 1>
 static int launch_tma_cfg(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len, uint4 *table, cudaStream_t st) {
-    using Cfg = StridedCfg<WARPS, NSTAGE>;
-    auto kern = md5_strided_tma_kernel<WARPS, MINB, NSTAGE, MODE>;
+    using Cfg = StridedCfg<WARPS, NSTAGE, TILES>;
+    auto kern = md5_strided_tma_kernel<WARPS, MINB, NSTAGE, MODE, TILES>;
     static thread_local int configured_dev = -1;
     int dev = 0;
     CU(cudaGetDevice(&dev));
@@ -401,6 +401,16 @@ static int launch_strided_tma(tpimd5_ctx *ctx, const void *base, uint64_t stride
                                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(TPIMD5_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
     int rc;
+    // Too few chains to fill the SMs (fewer than 16 warps per SM): every chain runs at its dependent-op
+    // latency, so pick the formulation with the shortest chain (mode 4: LOP3 -> IADD3 -> LEA.HI, all on
+    // one pipe) and the kernel shape with the least per-stage work on that chain.  Otherwise the
+    // integer pipes are the limit: mode 6 and the small-footprint shape.
+    const bool starved = n < (uint64_t)148 * 16 * 32;
+    if (shape == 0 && starved) {
+        rc = launch_tma_cfg<4, 3, 2, 4, 2>(tmap, n, (uint32_t)unit_len, table, st);
+        if (rc == 0) ctx->launches.fetch_add(1);
+        return rc;
+    }
 #define TPI_TMA(M)                                                                          \
     switch (shape) {                                                                        \
         case 1: rc = launch_tma_cfg<4, 4, 3, M>(tmap, n, (uint32_t)unit_len, table, st); break;  \
@@ -408,19 +418,14 @@ static int launch_strided_tma(tpimd5_ctx *ctx, const void *base, uint64_t stride
         case 2: rc = launch_tma_cfg<4, 5, 2, M>(tmap, n, (uint32_t)unit_len, table, st); break;  \
         case 3: rc = launch_tma_cfg<4, 3, 4, M>(tmap, n, (uint32_t)unit_len, table, st); break;  \
         case 4: rc = launch_tma_cfg<4, 6, 2, M>(tmap, n, (uint32_t)unit_len, table, st); break;  \
+        case 5: rc = launch_tma_cfg<4, 3, 2, M, 2>(tmap, n, (uint32_t)unit_len, table, st); break; \
+        case 6: rc = launch_tma_cfg<4, 1, 2, M, 4>(tmap, n, (uint32_t)unit_len, table, st); break; \
+        case 7: rc = launch_tma_cfg<4, 2, 3, M, 2>(tmap, n, (uint32_t)unit_len, table, st); break; \
     }
     if (mode == 0) {
         TPI_TMA(0)
-    } else if (mode == 5) {
-        TPI_TMA(5)
     } else if (mode == 6) {
         TPI_TMA(6)
-    } else if (mode == 7) {
-        TPI_TMA(7)
-    } else if (mode == 8) {
-        TPI_TMA(8)
-    } else if (mode == 9) {
-        TPI_TMA(9)
     } else {
         TPI_TMA(4)
     }
