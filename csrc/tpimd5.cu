@@ -448,6 +448,9 @@ static int launch_lanes(tpimd5_ctx *ctx, const LaneArgs &a0, bool aligned, cudaS
     a.one = 1u;
     int loader, mode, shape;
     decode_variant(ctx->variant.load(), loader, mode, shape);
+    // library default: too few chains to fill the SMs -> the formulation with the shortest dependent
+    // chain (mode 4); enough of them -> the one that spreads the additions over both integer pipes (6)
+    if (ctx->variant.load() == 0 && a.n < (uint64_t)148 * 16 * 32) mode = 4;
     int rc;
     if (aligned) {
         switch (mode) {
@@ -871,30 +874,51 @@ static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint
             if (used > shift) CU(cudaMemcpyAsync(s.d_stage[bi] + shift, job.base + lo, used - shift, cudaMemcpyHostToDevice, s.s_copy));
         } else {
             uint8_t *stage = s.h_stage[bi];
-            std::function<void(size_t)> fill = [&](size_t i) {
-                const Piece &p = pieces[i];
-                const uint32_t u = units[p.unit];
-                if (!p.len && !from_files) return;
-                if (from_files) {
-                    int fd = open(job.paths[u], O_RDONLY | O_CLOEXEC);
-                    const uint64_t fo = job.file_off ? job.file_off[u] : 0;
-                    // The listing promised exactly job.len[u] bytes.  Whole files are read with one byte
-                    // to spare (the packer leaves that byte free): getting it means the file grew.
-                    const bool probe = p.last && !job.file_off;
-                    int r = fd < 0 ? -1 : read_fully(fd, stage + p.dst, fo + p.src_off, p.len, probe);
-                    if (fd >= 0) close(fd);
-                    if (r != 0) {
-                        int expect = 0;
-                        if (io_err.compare_exchange_strong(expect, r == -1 ? errno ? errno : EIO : (r == -2 ? -2 : -3))) io_idx = u;
-                    }
+            // Work items are byte ranges, not units: a large file is read by several workers at once
+            // (pread at different offsets), a run of tiny ones by a single worker.
+            struct Task { uint32_t first, count; uint64_t lo, hi; };      // pieces [first, first+count); byte range of a lone piece
+            constexpr uint64_t CHUNK = 2u << 20;
+            std::vector<Task> tasks;
+            for (size_t i = 0; i < np;) {
+                if (pieces[i].len > CHUNK) {
+                    for (uint64_t lo = 0; lo < pieces[i].len; lo += CHUNK)
+                        tasks.push_back({(uint32_t)i, 1, lo, std::min<uint64_t>(pieces[i].len, lo + CHUNK)});
+                    ++i;
                 } else {
-                    memcpy(stage + p.dst, job.base + job.off[u] + p.src_off, p.len);
+                    size_t j = i;
+                    uint64_t bytes = 0;
+                    while (j < np && pieces[j].len <= CHUNK && bytes < CHUNK && j - i < 64) bytes += pieces[j++].len;
+                    tasks.push_back({(uint32_t)i, (uint32_t)(j - i), 0, 0});
+                    i = j;
+                }
+            }
+            auto fail_io = [&](int r, uint32_t u) {
+                int expect = 0;
+                if (io_err.compare_exchange_strong(expect, r == -1 ? (errno ? errno : EIO) : r)) io_idx = u;
+            };
+            std::function<void(size_t)> fill = [&](size_t t) {
+                const Task &tk = tasks[t];
+                for (uint32_t i = tk.first; i < tk.first + tk.count; ++i) {
+                    const Piece &p = pieces[i];
+                    const uint32_t u = units[p.unit];
+                    const bool whole = tk.count > 1 || tk.hi == 0;               // the piece in one go
+                    const uint64_t lo = whole ? 0 : tk.lo, hi = whole ? p.len : tk.hi;
+                    if (!from_files) {
+                        if (hi > lo) memcpy(stage + p.dst + lo, job.base + job.off[u] + p.src_off + lo, hi - lo);
+                        continue;
+                    }
+                    int fd = open(job.paths[u], O_RDONLY | O_CLOEXEC);
+                    if (fd < 0) { fail_io(-1, u); continue; }
+                    const uint64_t fo = job.file_off ? job.file_off[u] : 0;
+                    // The listing promised exactly job.len[u] bytes.  The end of a whole file is read with
+                    // one byte to spare (the packer leaves that byte free): getting it means the file grew.
+                    const bool probe = p.last && !job.file_off && hi == p.len;
+                    const int r = read_fully(fd, stage + p.dst + lo, fo + p.src_off + lo, hi - lo, probe);
+                    close(fd);
+                    if (r != 0) fail_io(r, u);
                 }
             };
-            // grain: a few MiB of copying or a handful of files per task
-            size_t grain = from_files ? 8 : std::max<size_t>(1, np / (size_t)(8 * (ctx->pool->size() + 1)));
-            if (!from_files && np < 64) grain = 1;
-            ctx->pool->parallel_for(np, grain, fill);
+            ctx->pool->parallel_for(tasks.size(), 1, fill);
             if (io_err.load() != 0) break;
             if (used) CU(cudaMemcpyAsync(s.d_stage[bi], stage, used, cudaMemcpyHostToDevice, s.s_copy));
         }
