@@ -466,8 +466,8 @@ def main():
             ms = e0.elapsed_time(e1) / 10
             print(json.dumps({"variant": variant, "ms": round(ms, 4), "GBps": round(nbytes / ms / 1e6, 1)}), flush=True)
         probe_out = torch.empty(148 * 16 * 128 * 16, dtype=torch.uint8, device=dev)
-        for mode in range(7):
-            for ctas in (4, 5, 8):
+        for mode in (0, 4, 5, 6):
+            for ctas in (4, 8):
                 ctx.dev_int_probe(mode, ctas, 64, probe_out, stream=stream)
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 torch.cuda.synchronize()

@@ -5,9 +5,8 @@
 // [rclone] fs/hash StreamTypes (reached from /root/reference/task/common/machine/storage.go:158).
 // Message words are little-endian, so bytes staged in shared memory are used as they are.
 //
-// Instruction budget per step: one LOP3 (F/G/H/I are single 3-input LUT ops), one SHF.L.W rotate
-// and three additions.  `m + k` does not depend on the chain and `a + (m + k)` only on a value
-// that was final three steps earlier, so the dependent chain per step is LOP3 -> add -> SHF -> add.
+// Instruction budget per step: one LOP3 (F/G/H/I are single 3-input LUT ops), the rotate fused with
+// the final addition into one LEA.HI, and the sum a + f + m + k (see the step modes below).
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -30,29 +29,19 @@ __device__ __forceinline__ uint32_t fH(uint32_t b, uint32_t c, uint32_t d) { ret
 __device__ __forceinline__ uint32_t fI(uint32_t b, uint32_t c, uint32_t d) { return lop3<0x39>(b, c, d); }  // c^(b|~d)
 
 // How the three additions of a step are issued.  sm_100a has two integer-capable pipes per SM
-// sub-partition (alu: LOP3/IADD3/SHF/LEA, fma: IMAD), each taking one warp instruction every other
-// cycle.  LOP3 and the fused rotate-add (LEA.HI) must go to alu; the additions can go either way,
-// but only if the compiler is stopped from folding them back into IADD3: `mad.lo` by a register
-// that holds 1 (`one`, a kernel argument the compiler cannot see through) is an add on the fma pipe.
-//   MODE 0  plain C, ptxas decides (it emits LOP3, IADD3, VIADD, LEA.HI: four alu ops, 8 cycles/step)
-//   MODE 1  m+k on fma, a+x+f as one IADD3 on alu          -> alu 3, fma 1
-//   MODE 3  m+k, a+x and y+f all on fma                    -> alu 2, fma 3
-//   MODE 2  steps alternate between 1 and 3                -> alu 2.5, fma 2 on average
-__device__ __forceinline__ uint32_t mad1(uint32_t a, uint32_t one, uint32_t c) {
-    uint32_t r;
-    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(one), "r"(c));
-    return r;
-}
-
-//   MODE 4  like 1, but m+k as a plain add hidden from the optimiser (VIADD reg+imm: one register read)
-//   MODE 5  like 3, with the multiplier 1 read from the constant bank instead of a register
-//   MODE 6  steps alternate between 4 and 5 (every second step adds on the fma pipe)
-//   MODE 7  every third step on the fma pipe, MODE 8  two of three, MODE 9  one of four
-// fma_step<MODE>(i): does step i (0..63) of a mixed mode take the fma-pipe form?
-template <int MODE>
-__host__ __device__ constexpr int fma_step(int i) {
-    return MODE == 2 || MODE == 6 ? (i & 1) : MODE == 7 ? (i % 3 == 0) : MODE == 8 ? (i % 3 != 0) : MODE == 9 ? (i % 4 == 0) : 0;
-}
+// sub-partition: alu (LOP3, IADD3, LEA, SHF; one warp instruction every other cycle) and fma (IMAD,
+// and the reg+imm VIADD).  LOP3 and the fused rotate-add (LEA.HI) must go to alu; the additions can go
+// either way, but ptxas, left alone, folds them into one IADD3 on alu and puts the constant add on the
+// dependent chain.  The step modes below were measured with the register-only probe and in the kernels
+// (profiles/r1_int_probe_modes0-6.jsonl):
+//   MODE 0  plain C, ptxas decides: LOP3 -> IADD3 -> VIADD -> LEA.HI, a four-deep chain
+//   MODE 4  m + k as a plain add hidden from the optimiser (VIADD, off the chain), then a + x + f as one
+//           IADD3: the three-deep chain LOP3 -> IADD3 -> LEA.HI, all on alu.  Shortest latency per step:
+//           used when chains are scarce.
+//   MODE 5  m + k as in 4; a + x and y + f as two IMADs by a 1 held in the constant bank / a uniform
+//           register (two register reads each) on the fma pipe: alu 2, fma 3 per step
+//   MODE 6  steps alternate between 4 and 5: alu 2.5, fma 2 on average.  Highest throughput: default
+//           when the SMs are full.
 __constant__ uint32_t c_one = 1u;
 
 __device__ __forceinline__ uint32_t add_imm(uint32_t a, uint32_t k) {
@@ -66,36 +55,35 @@ __device__ __forceinline__ uint32_t madc(uint32_t a, uint32_t c) {
     return r;
 }
 
-template <int MODE, int STEP_PARITY>
-__device__ __forceinline__ uint32_t step_sum(uint32_t a, uint32_t f, uint32_t m, uint32_t k, uint32_t one) {
+// does step i (0..63) of a mixed mode take the fma-pipe form?
+template <int MODE>
+__host__ __device__ constexpr int fma_step(int i) {
+    return MODE == 5 ? 1 : MODE == 6 ? (i & 1) : 0;
+}
+
+template <int MODE, int FMA_FORM>
+__device__ __forceinline__ uint32_t step_sum(uint32_t a, uint32_t f, uint32_t m, uint32_t k) {
     if (MODE == 0) {
         return (a + (m + k)) + f;
-    } else if (MODE == 4 || (MODE >= 6 && STEP_PARITY == 0)) {
+    } else if (!FMA_FORM) {
         const uint32_t x = add_imm(m, k);
         return a + x + f;
-    } else if (MODE >= 5) {
+    } else {
         const uint32_t x = add_imm(m, k);
         const uint32_t y = madc(a, x);
         return madc(f, y);
-    } else if (MODE == 1 || (MODE == 2 && STEP_PARITY == 0)) {
-        const uint32_t x = mad1(m, one, k);
-        return a + x + f;
-    } else {
-        const uint32_t x = mad1(m, one, k);
-        const uint32_t y = mad1(a, one, x);
-        return mad1(f, one, y);
     }
 }
 
 #define TPI_STEP(f, a, b, c, d, m, k, s, idx)                                    \
     {                                                                            \
-        const uint32_t t_ = step_sum<MODE, fma_step<MODE>(idx)>((a), f((b), (c), (d)), (m), (uint32_t)(k), one); \
+        const uint32_t t_ = step_sum<MODE, fma_step<MODE>(idx)>((a), f((b), (c), (d)), (m), (uint32_t)(k)); \
         (a) = (b) + rotl(t_, (s));                                               \
     }
 
 // One 64-byte block: st <- compress(st, m[0..15]).
 template <int MODE>
-__device__ __forceinline__ void md5_block(uint32_t (&st)[4], const uint32_t (&m)[16], uint32_t one) {
+__device__ __forceinline__ void md5_block(uint32_t (&st)[4], const uint32_t (&m)[16]) {
     uint32_t a = st[0], b = st[1], c = st[2], d = st[3];
     // round 1: g = i
     TPI_STEP(fF, a, b, c, d, m[0], 0xd76aa478u, 7, 0)

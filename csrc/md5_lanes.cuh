@@ -35,7 +35,6 @@ struct LaneArgs {
     const uint32_t *out_idx;   // unit -> row of `table` (nullptr: identity)
     uint4 *table;              // 16-byte chaining values / digests
     uint64_t n;                // units in this launch
-    uint32_t one;              // the value 1, opaque to the compiler (see md5_device.cuh step modes)
 };
 
 __device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void *gptr) {
@@ -208,7 +207,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) md5_lanes_kernel(const LaneA
             uint32_t m[16];
             const uint32_t src = src0 + j * 64u;
             load_block_words<ALIGNED>(src, sh, m);
-            md5_block<MODE>(st, m, p.one);
+            md5_block<MODE>(st, m);
         }
         __syncwarp();
     }
@@ -233,7 +232,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) md5_lanes_kernel(const LaneA
                 for (int q = 0; q < 16; ++q) m[q] = 0;
             }
             if (fin && b >= bm) md5_pad_block(m, (uint32_t)(len & 63u), b > bm, total);
-            md5_block<MODE>(st, m, p.one);
+            md5_block<MODE>(st, m);
         }
         if (j == BPS - 1) __syncwarp();  // every thread is done with this stage before it is refilled
     }
@@ -278,7 +277,7 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 // a register-only microbenchmark of the same instruction mix").
 // ---------------------------------------------------------------------------------------------
 template <int MODE>
-__global__ void __launch_bounds__(128) int_probe_kernel(uint32_t iters, uint32_t one, uint4 *__restrict__ out) {
+__global__ void __launch_bounds__(128) int_probe_kernel(uint32_t iters, uint4 *__restrict__ out) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t st[4], m[16];
     md5_iv(st);
@@ -287,7 +286,7 @@ __global__ void __launch_bounds__(128) int_probe_kernel(uint32_t iters, uint32_t
     for (int i = 0; i < 16; ++i) m[i] = t * 0x9E3779B9u + i;
 #pragma unroll 1
     for (uint32_t it = 0; it < iters; ++it) {
-        md5_block<MODE>(st, m, one);
+        md5_block<MODE>(st, m);
         m[0] ^= st[0];
     }
     out[t] = make_uint4(st[0], st[1], st[2], st[3]);

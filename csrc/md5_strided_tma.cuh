@@ -44,8 +44,7 @@ struct StridedCfg {
 
 template <int WARPS, int MINB, int NSTAGE, int MODE, int TILES = 1>
 __global__ void __launch_bounds__(WARPS * 32, MINB)
-md5_strided_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uint32_t unit_len, uint4 *__restrict__ table,
-                       uint32_t one) {
+md5_strided_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uint32_t unit_len, uint4 *__restrict__ table) {
     using Cfg = StridedCfg<WARPS, NSTAGE, TILES>;
     constexpr uint32_t SB = 128u * TILES;                     // bytes of one unit per stage
     constexpr uint32_t BPS = 2u * TILES;                      // MD5 blocks per stage
@@ -121,7 +120,7 @@ md5_strided_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uin
                                  : "r"(tile + xo[q]));
             }
 #pragma unroll
-            for (int k = 0; k < GROUP * 2; ++k) md5_block<MODE>(st, m[k], one);
+            for (int k = 0; k < GROUP * 2; ++k) md5_block<MODE>(st, m[k]);
         }
         __syncwarp();                                         // all 32 rows consumed before the buffer is refilled
     }
@@ -148,7 +147,7 @@ md5_strided_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uin
             for (int q = 0; q < 16; ++q) m[q] = 0;
         }
         if (b >= bm) md5_pad_block(m, unit_len & 63u, b > bm, (uint64_t)unit_len);
-        md5_block<MODE>(st, m, one);
+        md5_block<MODE>(st, m);
         if (within == BPS - 1) __syncwarp();
     }
     if (u < n) table[u] = make_uint4(st[0], st[1], st[2], st[3]);

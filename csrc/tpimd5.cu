@@ -383,7 +383,7 @@ static int launch_tma_cfg(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len
     }
     const uint64_t per_cta = WARPS * 32;
     const uint64_t grid = (n + per_cta - 1) / per_cta;
-    kern<<<(unsigned)grid, WARPS * 32, Cfg::SMEM_BYTES, st>>>(tmap, n, unit_len, table, 1u);
+    kern<<<(unsigned)grid, WARPS * 32, Cfg::SMEM_BYTES, st>>>(tmap, n, unit_len, table);
     CU(cudaGetLastError());
     return 0;
 }
@@ -445,7 +445,6 @@ static void decode_variant(int v, int &loader, int &mode, int &shape) {
 static int launch_lanes(tpimd5_ctx *ctx, const LaneArgs &a0, bool aligned, cudaStream_t st) {
     if (a0.n == 0) return 0;
     LaneArgs a = a0;
-    a.one = 1u;
     int loader, mode, shape;
     decode_variant(ctx->variant.load(), loader, mode, shape);
     // library default: too few chains to fill the SMs -> the formulation with the shortest dependent
@@ -652,7 +651,7 @@ extern "C" int tpimd5_dev_synth_fill(tpimd5_ctx *ctx, int slot, void *d_out, uin
 extern "C" int tpimd5_dev_int_probe(tpimd5_ctx *ctx, int slot, int mode, int ctas_per_sm, uint32_t iters, void *d_out,
                                     uint64_t *blocks_out, void *cuda_stream) {
     Slot *s = get_slot(ctx, slot);
-    if (!s || !d_out || ctas_per_sm < 1 || ctas_per_sm > 16 || mode < 0 || mode > 6)
+    if (!s || !d_out || ctas_per_sm < 1 || ctas_per_sm > 16 || (mode != 0 && mode != 4 && mode != 5 && mode != 6))
         return fail(TPIMD5_EINVAL, "dev_int_probe: bad argument");
     CU(cudaSetDevice(s->dev));
     int sms = 0;
@@ -660,13 +659,10 @@ extern "C" int tpimd5_dev_int_probe(tpimd5_ctx *ctx, int slot, int mode, int cta
     const unsigned grid = (unsigned)(sms * ctas_per_sm);
     cudaStream_t st = (cudaStream_t)cuda_stream;
     switch (mode) {
-        case 0: int_probe_kernel<0><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
-        case 1: int_probe_kernel<1><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
-        case 2: int_probe_kernel<2><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
-        case 3: int_probe_kernel<3><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
-        case 4: int_probe_kernel<4><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
-        case 5: int_probe_kernel<5><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
-        default: int_probe_kernel<6><<<grid, 128, 0, st>>>(iters, 1u, (uint4 *)d_out); break;
+        case 0: int_probe_kernel<0><<<grid, 128, 0, st>>>(iters, (uint4 *)d_out); break;
+        case 4: int_probe_kernel<4><<<grid, 128, 0, st>>>(iters, (uint4 *)d_out); break;
+        case 5: int_probe_kernel<5><<<grid, 128, 0, st>>>(iters, (uint4 *)d_out); break;
+        default: int_probe_kernel<6><<<grid, 128, 0, st>>>(iters, (uint4 *)d_out); break;
     }
     CU(cudaGetLastError());
     ctx->launches.fetch_add(1);
@@ -1309,13 +1305,13 @@ extern "C" int tpimd5_dev_s3_etag_noalloc(int device, const void *d_data, uint64
     // per-part MD5s into the built-in array (one lane per part) ...
     LaneArgs a{};
     a.base = (const uint8_t *)d_data; a.base_bytes = size; a.stride = part_size;
-    a.table = (uint4 *)parts; a.n = np; a.one = 1u;
+    a.table = (uint4 *)parts; a.n = np;
     const bool aligned = ((uintptr_t)d_data & 15) == 0 && (part_size & 15) == 0;
     int rc = aligned ? launch_cfg<128, true, 4, 5, 0>(a, st) : launch_cfg<128, false, 4, 5, 0>(a, st);
     if (rc) return rc;
     // ... then the MD5 of those 16*np bytes, read back from the same array
     LaneArgs b{};
     b.base = parts; b.base_bytes = np * 16; b.stride = np * 16;
-    b.table = (uint4 *)d_etag_md5_out; b.n = 1; b.one = 1u;
+    b.table = (uint4 *)d_etag_md5_out; b.n = 1;
     return launch_cfg<128, true, 4, 5, 0>(b, st);
 }
