@@ -531,9 +531,9 @@ def main():
         host_np = host.numpy()
         off = np.arange(n, dtype=np.uint64) * flen
         ln = np.full(n, flen, dtype=np.uint64)
-        out = None
+        out = np.empty((n, 16), dtype=np.uint8)            # reused across calls, as a caller's digest slice would be
         for _ in range(2):
-            out = ctx.hash_buffers(host_np, off, ln)
+            ctx.hash_buffers(host_np, off, ln, out=out)
         if not np.array_equal(out, digests.cpu().numpy()):
             raise SystemExit("bench.py: end-to-end digests differ from the kernel-only digests")
         # ceiling of this leg: the same pinned buffer copied to the device and nothing else (all ranks
@@ -552,7 +552,7 @@ def main():
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.e2e_steps):
-            out = ctx.hash_buffers(host_np, off, ln)
+            ctx.hash_buffers(host_np, off, ln, out=out)
         barrier()
         dt = max_over_ranks(time.perf_counter() - t0)
         e2e = {"value": round(world * nbytes * args.e2e_steps / dt / 1e9, 3), "unit": "GB/s",

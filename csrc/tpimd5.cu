@@ -163,7 +163,6 @@ struct Slot {
     bool staged = false;
     uint8_t *h_stage[NBUF] = {}, *d_stage[NBUF] = {};
     uint8_t *h_desc_raw[NBUF] = {}, *d_desc_raw[NBUF] = {};
-    LaneDesc hd[NBUF], dd[NBUF];
     cudaEvent_t ev_copied[NBUF] = {}, ev_done[NBUF] = {};
     // digest / chaining-value table
     uint4 *d_table = nullptr;
@@ -223,8 +222,6 @@ static int ensure_staging(tpimd5_ctx *ctx, Slot &s) {
         CU(cudaMalloc(&s.d_stage[i], s.stage_bytes + 256));
         CU(cudaHostAlloc(&s.h_desc_raw[i], MAX_BATCH_LANES * desc_bytes_per_lane, cudaHostAllocDefault));
         CU(cudaMalloc(&s.d_desc_raw[i], MAX_BATCH_LANES * desc_bytes_per_lane));
-        carve_desc(s.h_desc_raw[i], MAX_BATCH_LANES, s.hd[i]);
-        carve_desc(s.d_desc_raw[i], MAX_BATCH_LANES, s.dd[i]);
         CU(cudaEventCreateWithFlags(&s.ev_copied[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&s.ev_done[i], cudaEventDisableTiming));
     }
@@ -848,7 +845,10 @@ static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint
         bool ragged = false;
         for (size_t i = 1; i < np && !ragged; ++i) ragged = (pieces[i].len >> 6) != (pieces[0].len >> 6);
         if (ragged) std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return pieces[a].len > pieces[b].len; });
-        LaneDesc &h = s.hd[bi];
+        // the five descriptor arrays are carved for exactly np lanes, so they are one contiguous copy
+        LaneDesc h, dv;
+        carve_desc(s.h_desc_raw[bi], np, h);
+        carve_desc(s.d_desc_raw[bi], np, dv);
         bool aligned = true;
         for (size_t i = 0; i < np; ++i) {
             const Piece &p = pieces[order[i]];
@@ -919,11 +919,7 @@ static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint
             if (used) CU(cudaMemcpyAsync(s.d_stage[bi], stage, used, cudaMemcpyHostToDevice, s.s_copy));
         }
         // descriptors: five arrays, copied as stored (their device mirror has the same carving)
-        CU(cudaMemcpyAsync(s.dd[bi].off, h.off, np * 8, cudaMemcpyHostToDevice, s.s_copy));
-        CU(cudaMemcpyAsync(s.dd[bi].len, h.len, np * 8, cudaMemcpyHostToDevice, s.s_copy));
-        CU(cudaMemcpyAsync(s.dd[bi].prior, h.prior, np * 8, cudaMemcpyHostToDevice, s.s_copy));
-        CU(cudaMemcpyAsync(s.dd[bi].flags, h.flags, np * 4, cudaMemcpyHostToDevice, s.s_copy));
-        CU(cudaMemcpyAsync(s.dd[bi].oidx, h.oidx, np * 4, cudaMemcpyHostToDevice, s.s_copy));
+        if (np) CU(cudaMemcpyAsync(s.d_desc_raw[bi], s.h_desc_raw[bi], np * desc_bytes_per_lane, cudaMemcpyHostToDevice, s.s_copy));
         CU(cudaEventRecord(s.ev_copied[bi], s.s_copy));
 
         // ---- hash ------------------------------------------------------------------------------
@@ -933,8 +929,8 @@ static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint
         if (batch > 0 && np && pieces[0].src_off > 0) CU(cudaStreamWaitEvent(sk, s.ev_done[(batch - 1) % NBUF], 0));
         LaneArgs a{};
         a.base = s.d_stage[bi]; a.base_bytes = used;
-        a.off = s.dd[bi].off; a.len = s.dd[bi].len; a.prior = s.dd[bi].prior;
-        a.flags = s.dd[bi].flags; a.out_idx = s.dd[bi].oidx;
+        a.off = dv.off; a.len = dv.len; a.prior = dv.prior;
+        a.flags = dv.flags; a.out_idx = dv.oidx;
         a.table = s.d_table; a.n = np;
         rc = launch_lanes(ctx, a, aligned, sk);
         if (rc) return rc;

@@ -224,13 +224,17 @@ class Context:
             pass
 
     # ---- host-memory entry points -----------------------------------------------------------
-    def hash_buffers(self, base, offsets, lengths) -> np.ndarray:
-        """MD5 of each (offset, length) unit of `base` -> uint8[n, 16]."""
+    def hash_buffers(self, base, offsets, lengths, out: Optional[np.ndarray] = None) -> np.ndarray:
+        """MD5 of each (offset, length) unit of `base` -> uint8[n, 16] (into `out` if given, the way a Go
+        caller reuses its digest slice)."""
         off = np.ascontiguousarray(offsets, dtype=np.uint64)
         ln = np.ascontiguousarray(lengths, dtype=np.uint64)
         if off.shape != ln.shape or off.ndim != 1:
             raise ValueError("offsets and lengths must be 1-D and the same length")
-        out = np.empty((off.size, 16), dtype=np.uint8)
+        if out is None:
+            out = np.empty((off.size, 16), dtype=np.uint8)
+        elif out.dtype != np.uint8 or out.shape != (off.size, 16) or not out.flags["C_CONTIGUOUS"]:
+            raise ValueError("out must be a C-contiguous uint8[n, 16]")
         if isinstance(base, int):
             bp = base
         else:
