@@ -186,55 +186,57 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) md5_lanes_kernel(const LaneA
     const uint32_t myrow = wbase + lane * ROWB;
     const uint64_t total = prior + len;
 
-    // ---- phase A: stages in which all 32 units still have CH whole bytes -----------------------
-    // No tail logic, no per-thread predicates: copy, wait, 4 x LDS.128 and the 64 steps per block.
-    // (An unaligned unit needs CH+16 bytes for its shifted window, hence the "+ sh" below.)
+    // ---- stage loop ---------------------------------------------------------------------------------
+    // Per stage the warp votes: if every unit either has CH whole bytes left or is completely done
+    // (padding included), the stage runs without any tail logic -- copy, wait, 4 x LDS.128 and the 64
+    // steps per block, finished threads sitting out.  That is the whole run of a uniform batch and, in a
+    // length-sorted batch, everything except the stage in which a unit ends.  Only such a stage takes
+    // the per-block path that knows about partial blocks and padding.
+    // (An unaligned unit needs CH+16 bytes for its shifted window, hence the margins below.)
     const uint64_t full64 = (ALIGNED ? len : (len > sh ? len - sh : 0)) / CH;
     const uint32_t full_st = full64 > 0xffffffffull ? 0xffffffffu : (uint32_t)full64;
-    const uint32_t warp_fast = __reduce_min_sync(0xffffffffu, ALIGNED ? full_st : (full_st ? full_st - 1 : 0));
-    uint32_t s_done = 0;
+    const uint32_t my_whole = ALIGNED ? full_st : (full_st ? full_st - 1 : 0);   // stages this unit runs without tail logic
+    const uint32_t warp_fast = __reduce_min_sync(0xffffffffu, my_whole);          // ... and every unit of the warp does
+    const uint32_t stages_total = (warp_nb + BPS - 1) / BPS;
 #pragma unroll 1
-    for (; s_done < warp_fast; ++s_done) {
-        const uint32_t s = s_done;
-        if (s + 1 < warp_fast) issue_full(s + 1);
-        else if (s + 1 < warp_nst) issue(s + 1);
-        cp_async_commit();
-        cp_async_wait<1>();
-        __syncwarp();
-        const uint32_t src0 = myrow + (s & 1u) * Cfg::STAGE_BYTES;
-#pragma unroll 1
-        for (uint32_t j = 0; j < (uint32_t)BPS; ++j) {
-            uint32_t m[16];
-            const uint32_t src = src0 + j * 64u;
-            load_block_words<ALIGNED>(src, sh, m);
-            md5_block<MODE>(st, m);
-        }
-        __syncwarp();
-    }
-
-    // ---- phase B: ragged rest -- tails, padding blocks, units that have already finished --------
-#pragma unroll 1
-    for (uint32_t b = warp_fast * BPS; b < warp_nb; ++b) {
-        const uint32_t j = b % BPS, s = b / BPS;
-        if (j == 0 && s < warp_nst) {
-            if (s + 1 < warp_nst) issue(s + 1);
+    for (uint32_t s = 0; s < stages_total; ++s) {
+        if (s < warp_nst) {
+            if (s + 1 < warp_fast) issue_full(s + 1);
+            else if (s + 1 < warp_nst) issue(s + 1);
             cp_async_commit();
             cp_async_wait<1>();      // everything but the newest group: stage s has landed
             __syncwarp();
         }
-        if (b < nb) {
-            uint32_t m[16];
-            if (b <= bm && b < nst * BPS) {
-                const uint32_t src = myrow + (s & 1u) * Cfg::STAGE_BYTES + j * 64u;
-                load_block_words<ALIGNED>(src, sh, m);
-            } else {
-#pragma unroll
-                for (int q = 0; q < 16; ++q) m[q] = 0;
+        const bool whole = s < my_whole;
+        const bool over = (uint64_t)s * BPS >= nb;
+        const uint32_t src0 = myrow + (s & 1u) * Cfg::STAGE_BYTES;
+        if (__all_sync(0xffffffffu, whole || over)) {
+            if (whole) {
+#pragma unroll 1
+                for (uint32_t j = 0; j < (uint32_t)BPS; ++j) {
+                    uint32_t m[16];
+                    load_block_words<ALIGNED>(src0 + j * 64u, sh, m);
+                    md5_block<MODE>(st, m);
+                }
             }
-            if (fin && b >= bm) md5_pad_block(m, (uint32_t)(len & 63u), b > bm, total);
-            md5_block<MODE>(st, m);
+        } else {
+#pragma unroll 1
+            for (uint32_t j = 0; j < (uint32_t)BPS; ++j) {
+                const uint32_t b = s * BPS + j;
+                if (b < nb) {
+                    uint32_t m[16];
+                    if (b <= bm && b < nst * BPS) {
+                        load_block_words<ALIGNED>(src0 + j * 64u, sh, m);
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < 16; ++q) m[q] = 0;
+                    }
+                    if (fin && b >= bm) md5_pad_block(m, (uint32_t)(len & 63u), b > bm, total);
+                    md5_block<MODE>(st, m);
+                }
+            }
         }
-        if (j == BPS - 1) __syncwarp();  // every thread is done with this stage before it is refilled
+        __syncwarp();                // every thread is done with this stage before it is refilled
     }
     cp_async_wait<0>();
     if (valid) p.table[oidx] = make_uint4(st[0], st[1], st[2], st[3]);

@@ -446,7 +446,7 @@ static int launch_lanes(tpimd5_ctx *ctx, const LaneArgs &a0, bool aligned, cudaS
     decode_variant(ctx->variant.load(), loader, mode, shape);
     // library default: too few chains to fill the SMs -> the formulation with the shortest dependent
     // chain (mode 4); enough of them -> the one that spreads the additions over both integer pipes (6)
-    if (ctx->variant.load() == 0 && a.n < (uint64_t)148 * 16 * 32) mode = 4;
+    if (ctx->variant.load() == 0 && a.n < (uint64_t)148 * 16 * 32) { mode = 4; shape = 2; }   // + 256-byte stages: half the per-stage work
     int rc;
     if (aligned) {
         switch (mode) {
