@@ -330,16 +330,32 @@ def run_side_workload(args, torch, dist, tpi, ctx, dev, rank, world, barrier, ma
     elif args.workload == "c3":
         size, part, files = 64 << 30, 8 << 20, 8
         mine = [f for f in range(files) if f % world == rank]
-        data = torch.empty(size, dtype=torch.uint8, device=dev)
-        ctx.dev_synth_fill(data, 3, rank, size, 1, stream=stream)
+        # One file has only 8,192 chains (a quarter of what fills the SMs), so two files are kept resident
+        # (128 of the 180 GB) and hashed concurrently on two streams whenever this rank has two or more.
+        resident = 2 if len(mine) >= 2 else 1
         nparts = tpi.s3_nparts(size, part)
-        parts = torch.empty((nparts, 16), dtype=torch.uint8, device=dev)
-        etag = torch.empty(16, dtype=torch.uint8, device=dev)
+        bufs, parts, etags, streams = [], [], [], []
+        for r in range(resident):
+            b = torch.empty(size, dtype=torch.uint8, device=dev)
+            ctx.dev_synth_fill(b, 3, rank * 2 + r, size, 1, stream=stream)
+            bufs.append(b)
+            parts.append(torch.empty((nparts, 16), dtype=torch.uint8, device=dev))
+            etags.append(torch.empty(16, dtype=torch.uint8, device=dev))
+            streams.append(torch.cuda.Stream(device=dev))
+        torch.cuda.synchronize()
 
         def step():
-            for _ in mine:                      # the same resident 64 GiB stands in for each of this rank's files
-                ctx.dev_s3_etag(data, size, part, etag, d_part_digests=parts, stream=stream)
-        work_bytes, label = files * size, "C3: 8 files x 64 GiB, S3 multipart ETag, 8 MiB parts (8,192 lanes per file + digest of digests)"
+            cur = torch.cuda.current_stream()
+            for st_ in streams:
+                st_.wait_stream(cur)
+            for i, _ in enumerate(mine):            # the resident buffers stand in, in turn, for this rank's files
+                r = i % resident
+                ctx.dev_s3_etag(bufs[r], size, part, etags[r], d_part_digests=parts[r], stream=streams[r].cuda_stream)
+            for st_ in streams:
+                cur.wait_stream(st_)
+        work_bytes = files * size
+        label = (f"C3: 8 files x 64 GiB, S3 multipart ETag, 8 MiB parts (8,192 lanes per file + digest of digests), "
+                 f"{resident} file(s) resident and in flight per GPU")
         scaling = "strong"
     else:
         n, flen = 25600, 4 << 20
