@@ -748,7 +748,7 @@ static int read_fully(int fd, uint8_t *dst, uint64_t off, uint64_t n, bool probe
 }
 
 // Runs one device's share of a job.  `units` are indices into the job.
-static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint32_t> &units_in) {
+static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint32_t> &units_in) {
     if (units_in.empty()) return 0;
     // Files: longest first.  One file is one serial chain (~125 MB/s), so the device's finish time is
     // bounded by its longest file; starting those in the first batch lets the short ones fill in behind.
@@ -758,7 +758,6 @@ static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint
         std::stable_sort(by_size.begin(), by_size.end(), [&](uint32_t a, uint32_t b) { return job.len[a] > job.len[b]; });
     }
     const std::vector<uint32_t> &units = job.paths ? by_size : units_in;
-    std::lock_guard<std::mutex> guard(s.mu);
     CU(cudaSetDevice(s.dev));
     int rc = ensure_staging(ctx, s);
     if (rc) return rc;
@@ -961,6 +960,22 @@ static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint
         i = j;
     }
     return 0;
+}
+
+// Runs one device's share under the slot's lock.  Whatever goes wrong, no copy out of caller memory and
+// no kernel is left in flight when this returns: the caller may free its buffers right away.
+static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint32_t> &units) {
+    std::lock_guard<std::mutex> guard(s.mu);
+    const int rc = run_device_impl(ctx, s, job, units);
+    if (rc != 0) {
+        const std::string keep = g_err;                 // the first error is the one to report
+        cudaSetDevice(s.dev);
+        cudaStreamSynchronize(s.s_copy);
+        for (int b = 0; b < NBUF; ++b)
+            if (s.s_batch[b]) cudaStreamSynchronize(s.s_batch[b]);
+        g_err = keep;
+    }
+    return rc;
 }
 
 static int run_job(tpimd5_ctx *ctx, Job &job) {

@@ -474,3 +474,26 @@ def test_more_units_than_one_batch_of_descriptors(ctx):
     got = ctx.hash_buffers(buf, off, ln)
     want = oracle.md5_batch(buf, off, ln, threads=8, engine=oracle.ENGINE_OPENSSL if oracle.lib().orc_has_openssl() else 0)
     assert np.array_equal(got, want)
+
+
+def test_bad_arguments_are_refused_with_a_message(ctx):
+    import torch
+    d = torch.zeros(4096, dtype=torch.uint8, device="cuda")
+    dig = torch.zeros((4, 16), dtype=torch.uint8, device="cuda")
+    cases = [
+        lambda: ctx.dev_hash_buffers(d, 4096, 4, dig, stride=0),                           # no stride, no offsets
+        lambda: ctx.dev_hash_buffers(d, 4096, 4, dig, stride=2048),                        # 4 units do not fit
+        lambda: ctx.dev_hash_buffers(d, 4096, 4, dig.view(-1)[1:], stride=1024),           # digests not 16-byte aligned
+        lambda: ctx.dev_hash_buffers(d, 4096, 4, dig, d_offsets=d),                        # offsets without lengths
+        lambda: ctx.dev_s3_etag(d, 4096, 0, dig),                                          # part size 0
+        lambda: ctx.dev_synth_fill(d, 1, 0, 24, 10),                                       # file_len not a multiple of 16
+        lambda: ctx.set_variant(1234),
+        lambda: tpi.Context([99]),                                                         # no such device
+        lambda: tpi.Context([0], staging_bytes=1000),                                      # staging below 1 MiB
+    ]
+    for i, f in enumerate(cases):
+        with pytest.raises(tpi.TpiMd5Error) as e:
+            f()
+        assert e.value.code in (-1, -2, -6) and len(str(e.value)) > 20, i
+    # and the context is still usable afterwards
+    assert ctx.hash_buffers(b"abc", [0], [3])[0].tobytes().hex() == "900150983cd24fb0d6963f7d28e17f72"
