@@ -413,6 +413,9 @@ def main():
         run_reference(args, rank, world)
         return 0
 
+    if not os.path.exists(os.path.join(ROOT, "terraform-provider-iterative_b200", "libtpimd5.so")) and rank == 0:
+        import __graft_entry__
+        __graft_entry__.build()          # normally prebuilt; never a fallback to anything but this library
     import torch
     import torch.distributed as dist
     import tpi_b200 as tpi
