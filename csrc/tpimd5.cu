@@ -776,6 +776,16 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
     // one H2D copy straight from there (full speed when the caller's buffer is pinned).  Otherwise
     // (scattered units, files) the pool packs units 16-byte aligned into pinned staging first.
     bool direct = !from_files;
+    if (direct && job.base) {
+        // Pageable caller memory (a Go slice, a numpy array): the driver would stage a direct copy through
+        // its own bounce buffers on one thread.  The worker pool packing into our pinned staging is faster.
+        cudaPointerAttributes attr;
+        const bool pinned = cudaPointerGetAttributes(&attr, job.base + job.off[units[0]]) == cudaSuccess &&
+                            (attr.type == cudaMemoryTypeHost || attr.type == cudaMemoryTypeManaged);
+        cudaGetLastError();
+        const char *force = getenv("TPIMD5_PAGEABLE_DIRECT");
+        if (!pinned && !(force && force[0] == '1')) direct = false;
+    }
     if (direct) {
         uint64_t bytes = 0;
         for (size_t i = 0; i < nu && direct; ++i) {

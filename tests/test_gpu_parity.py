@@ -497,3 +497,18 @@ def test_bad_arguments_are_refused_with_a_message(ctx):
         assert e.value.code in (-1, -2, -6) and len(str(e.value)) > 20, i
     # and the context is still usable afterwards
     assert ctx.hash_buffers(b"abc", [0], [3])[0].tobytes().hex() == "900150983cd24fb0d6963f7d28e17f72"
+
+
+def test_pinned_source_takes_the_direct_copy_path(ctx):
+    """Pageable caller memory is packed through pinned staging; a pinned buffer (what bench.py's e2e leg
+    and a cgo caller with C-allocated pinned memory pass) is copied straight from where it lies, for any
+    alignment of its units.  Same digests either way."""
+    import torch
+    lengths = [int(x) for x in np.random.default_rng(76).integers(0, 30000, 2000)] + [(20 << 20) + 5, 0, 64]
+    for align in (16, 1):
+        buf, off, ln = oracle.synth_packed(76, lengths, align=align)
+        pinned = torch.empty(buf.size, dtype=torch.uint8, pin_memory=True)
+        pinned.numpy()[:] = buf
+        want = oracle.md5_batch(buf, off, ln, threads=4)
+        assert np.array_equal(ctx.hash_buffers(pinned.numpy(), off, ln), want)        # direct
+        assert np.array_equal(ctx.hash_buffers(buf, off, ln), want)                   # packed
