@@ -680,6 +680,9 @@ struct Job {
     const uint64_t *len = nullptr;
     const char *const *paths = nullptr;
     const uint64_t *file_off = nullptr;    // with paths: unit i is bytes [file_off[i], +len[i]) of its file (S3 parts)
+    // streams: unit i is prefix[i][0..prefix_len[i]) followed by base+off[i]; len[i] counts both
+    const uint8_t *const *prefix = nullptr;
+    const uint64_t *prefix_len = nullptr;
     const uint8_t *init_states = nullptr;  // 16*n or null
     const uint64_t *prior = nullptr;       // or null
     const uint8_t *nonfinal = nullptr;     // per unit: 1 = leave as chaining value; or null
@@ -775,7 +778,7 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
     // Direct mode: units already lie close together and in order in caller memory, so each batch is
     // one H2D copy straight from there (full speed when the caller's buffer is pinned).  Otherwise
     // (scattered units, files) the pool packs units 16-byte aligned into pinned staging first.
-    bool direct = !from_files;
+    bool direct = !from_files && !job.prefix;
     if (direct && job.base) {
         // Pageable caller memory (a Go slice, a numpy array): the driver would stage a direct copy through
         // its own bounce buffers on one thread.  The worker pool packing into our pinned staging is faster.
@@ -909,7 +912,17 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
                     const bool whole = tk.count > 1 || tk.hi == 0;               // the piece in one go
                     const uint64_t lo = whole ? 0 : tk.lo, hi = whole ? p.len : tk.hi;
                     if (!from_files) {
-                        if (hi > lo) memcpy(stage + p.dst + lo, job.base + job.off[u] + p.src_off + lo, hi - lo);
+                        // logical bytes [a, b) of the unit: first its prefix (a stream's buffered bytes), then base+off
+                        const uint64_t P = job.prefix_len ? job.prefix_len[u] : 0;
+                        uint64_t a = p.src_off + lo;
+                        const uint64_t b = p.src_off + hi;
+                        uint8_t *dst = stage + p.dst + lo;
+                        if (a < P) {
+                            const uint64_t k = std::min(b, P) - a;
+                            memcpy(dst, job.prefix[u] + a, k);
+                            dst += k; a += k;
+                        }
+                        if (b > a) memcpy(dst, job.base + job.off[u] + (a - P), b - a);
                         continue;
                     }
                     int fd = open(job.paths[u], O_RDONLY | O_CLOEXEC);
@@ -1198,35 +1211,58 @@ extern "C" int tpimd5_stream_reset(tpimd5_stream *s) {
     return 0;
 }
 
-// Hash the whole blocks pending in each of `ss` in one launch; keeps < 64 bytes per stream.
-static int flush_streams(tpimd5_stream *const *ss, size_t n) {
+// Advance streams together, one lane each, one launch: stream i hashes the whole 64-byte blocks of
+// (its buffered bytes || ptrs[i][0..lens[i])) straight from where those bytes lie -- the buffered part is
+// the unit's prefix, the new data is not copied into the stream first -- and keeps the < 64 bytes left
+// over.  ptrs may be null (flush only).
+static int advance_streams(tpimd5_stream *const *ss, const void *const *ptrs, const size_t *lens, size_t n) {
     if (n == 0) return 0;
     tpimd5_ctx *ctx = ss[0]->ctx;
-    std::vector<uint64_t> off, len, prior;
+    std::vector<uint64_t> off, len, prior, plen;
+    std::vector<const uint8_t *> pfx;
     std::vector<uint8_t> init, nonfinal, out;
     std::vector<size_t> who;
+    static const uint8_t dummy = 0;
     for (size_t i = 0; i < n; ++i) {
-        const uint64_t full = ss[i]->pend.size() & ~(size_t)63;
-        if (!full) continue;
+        tpimd5_stream *s = ss[i];
+        const uint64_t add = ptrs ? lens[i] : 0;
+        const uint64_t total = s->pend.size() + add;
+        const uint64_t full = total & ~(uint64_t)63;
+        if (!full || (ptrs && add < 64 && s->pend.size() + add < STREAM_FLUSH)) {
+            // nothing worth a lane yet: buffer it (also keeps the left-over logic below simple: the tail of
+            // a hashed unit always lies inside the new data)
+            if (add) s->pend.insert(s->pend.end(), (const uint8_t *)ptrs[i], (const uint8_t *)ptrs[i] + add);
+            continue;
+        }
         who.push_back(i);
-        off.push_back((uint64_t)(uintptr_t)ss[i]->pend.data());
+        pfx.push_back(s->pend.empty() ? &dummy : s->pend.data());
+        plen.push_back(s->pend.size());
+        off.push_back(add ? (uint64_t)(uintptr_t)ptrs[i] : (uint64_t)(uintptr_t)&dummy);
         len.push_back(full);
-        prior.push_back(ss[i]->hashed);
-        init.insert(init.end(), ss[i]->state, ss[i]->state + 16);
+        prior.push_back(s->hashed);
+        init.insert(init.end(), s->state, s->state + 16);
         nonfinal.push_back(1);
     }
     if (who.empty()) return 0;
     out.resize(who.size() * 16);
     Job job;
     job.n = who.size(); job.base = nullptr; job.off = off.data(); job.len = len.data();
+    job.prefix = pfx.data(); job.prefix_len = plen.data();
     job.init_states = init.data(); job.prior = prior.data(); job.nonfinal = nonfinal.data(); job.out = out.data();
     int rc = run_job(ctx, job);
     if (rc) return rc;
     for (size_t k = 0; k < who.size(); ++k) {
-        tpimd5_stream *s = ss[who[k]];
+        const size_t i = who[k];
+        tpimd5_stream *s = ss[i];
+        const uint64_t add = ptrs ? lens[i] : 0, P = plen[k], total = P + add, left = total - len[k];
         memcpy(s->state, out.data() + 16 * k, 16);
         s->hashed += len[k];
-        s->pend.erase(s->pend.begin(), s->pend.begin() + (ptrdiff_t)len[k]);
+        // the unhashed tail: logical bytes [len[k], total) of (pend || new data)
+        std::vector<uint8_t> tail;
+        tail.reserve(64);
+        for (uint64_t x = len[k]; x < total; ++x) tail.push_back(x < P ? s->pend[x] : ((const uint8_t *)ptrs[i])[x - P]);
+        (void)left;
+        s->pend.swap(tail);
     }
     return 0;
 }
@@ -1234,38 +1270,31 @@ static int flush_streams(tpimd5_stream *const *ss, size_t n) {
 extern "C" int tpimd5_stream_write(tpimd5_stream *s, const void *p, size_t n) {
     if (!s || (!p && n)) return fail(TPIMD5_EINVAL, "stream_write: null pointer");
     std::lock_guard<std::mutex> g(s->mu);
-    const uint8_t *b = (const uint8_t *)p;
-    while (n) {
-        const size_t room = STREAM_FLUSH > s->pend.size() ? STREAM_FLUSH - s->pend.size() : 0;
-        const size_t take = std::min(n, std::max<size_t>(room, 64));
-        s->pend.insert(s->pend.end(), b, b + take);
-        b += take; n -= take;
-        if (s->pend.size() >= STREAM_FLUSH) {
-            tpimd5_stream *one = s;
-            int rc = flush_streams(&one, 1);
-            if (rc) return rc;
-        }
+    // Small writes (io.Copy hands over 32 KiB at a time) are buffered up to STREAM_FLUSH so that a launch
+    // always has megabytes to chew on; a large write goes to the GPU from where it lies.
+    if (s->pend.size() + n < STREAM_FLUSH) {
+        s->pend.insert(s->pend.end(), (const uint8_t *)p, (const uint8_t *)p + n);
+        return 0;
     }
-    return 0;
+    tpimd5_stream *one = s;
+    const void *ptr = p;
+    return advance_streams(&one, &ptr, &n, 1);
 }
 
 extern "C" int tpimd5_stream_write_many(tpimd5_stream *const *streams, const void *const *ptrs, const size_t *lens,
                                         size_t n_streams) {
     if (n_streams == 0) return 0;
     if (!streams || !ptrs || !lens) return fail(TPIMD5_EINVAL, "stream_write_many: null pointer");
+    {
+        std::vector<const tpimd5_stream *> seen(streams, streams + n_streams);
+        std::sort(seen.begin(), seen.end());
+        if (std::adjacent_find(seen.begin(), seen.end()) != seen.end()) return fail(TPIMD5_EINVAL, "stream_write_many: stream listed twice");
+    }
     for (size_t i = 0; i < n_streams; ++i) {
         if (!streams[i] || (!ptrs[i] && lens[i])) return fail(TPIMD5_EINVAL, "stream_write_many: null entry %zu", i);
         if (streams[i]->ctx != streams[0]->ctx) return fail(TPIMD5_EINVAL, "stream_write_many: streams of different contexts");
-        for (size_t k = 0; k < i; ++k)
-            if (streams[k] == streams[i]) return fail(TPIMD5_EINVAL, "stream_write_many: stream listed twice");
     }
-    // append everything, then advance all streams together (one lane each, one launch)
-    for (size_t i = 0; i < n_streams; ++i) {
-        std::lock_guard<std::mutex> g(streams[i]->mu);
-        const uint8_t *b = (const uint8_t *)ptrs[i];
-        streams[i]->pend.insert(streams[i]->pend.end(), b, b + lens[i]);
-    }
-    return flush_streams(streams, n_streams);
+    return advance_streams(streams, ptrs, lens, n_streams);
 }
 
 extern "C" int tpimd5_stream_sum(tpimd5_stream *s, uint8_t out[16]) {

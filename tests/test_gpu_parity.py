@@ -512,3 +512,34 @@ def test_pinned_source_takes_the_direct_copy_path(ctx):
         want = oracle.md5_batch(buf, off, ln, threads=4)
         assert np.array_equal(ctx.hash_buffers(pinned.numpy(), off, ln), want)        # direct
         assert np.array_equal(ctx.hash_buffers(buf, off, ln), want)                   # packed
+
+
+def test_streams_mixed_write_paths_randomised(ctx):
+    """Small buffered writes, large zero-copy writes and grouped writes on the same streams, in random
+    order, with Sum taken in between: always what hashlib gives for the bytes written so far."""
+    rng = np.random.default_rng(77)
+    n = 12
+    streams = [ctx.stream() for _ in range(n)]
+    ref = [hashlib.md5() for _ in range(n)]
+    sizes = [0, 1, 63, 64, 65, 1000, 40000, (4 << 20) - 1, 4 << 20, (5 << 20) + 3]
+    pool = rng.integers(0, 256, 6 << 20, dtype=np.uint8)
+    for step in range(40):
+        if rng.random() < 0.5:
+            i = int(rng.integers(0, n))
+            k = int(rng.choice(sizes))
+            o = int(rng.integers(0, pool.size - k))
+            streams[i].write(pool[o:o + k]); ref[i].update(pool[o:o + k].tobytes())
+        else:
+            who = sorted(rng.choice(n, int(rng.integers(1, n + 1)), replace=False).tolist())
+            chunks = []
+            for i in who:
+                k = int(rng.choice(sizes[:8]))
+                o = int(rng.integers(0, pool.size - k))
+                chunks.append(pool[o:o + k]); ref[i].update(pool[o:o + k].tobytes())
+            ctx.stream_write_many([streams[i] for i in who], chunks)
+        if step % 5 == 4:
+            j = int(rng.integers(0, n))
+            assert streams[j].sum() == ref[j].digest(), (step, j)
+    for s, r in zip(streams, ref):
+        assert s.sum() == r.digest()
+        s.close()
