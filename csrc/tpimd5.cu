@@ -1011,10 +1011,26 @@ static int run_job(tpimd5_ctx *ctx, Job &job) {
         shard_lpt(job.len, job.n, 1, shards);
         return run_device(ctx, *ctx->slots[0], job, shards[0]);
     }
-    shard_lpt(job.len, job.n, ndev, shards);
-    // direct mode wants ascending addresses; LPT order is by size.  Re-sort each shard by the
-    // caller's order (for files that is listing order, which is also friendliest to the page cache).
-    for (auto &v : shards) std::sort(v.begin(), v.end());
+    // Unless the sizes are heavy-tailed, cut the caller's order into ndev runs of equal bytes: every device
+    // then gets one dense stretch of the caller's buffer (direct copies, no packing) and the imbalance is at
+    // most one unit.  A unit bigger than a quarter of a device's share means the tail matters: greedy LPT.
+    uint64_t total = 0, biggest = 0;
+    for (size_t i = 0; i < job.n; ++i) { total += job.len[i] + 72; biggest = std::max(biggest, job.len[i]); }
+    if (biggest <= total / (4 * (uint64_t)ndev)) {
+        shards.assign(ndev, {});
+        uint64_t acc = 0;
+        int d = 0;
+        for (size_t i = 0; i < job.n; ++i) {
+            while (d + 1 < ndev && acc >= (total / ndev) * (uint64_t)(d + 1)) ++d;
+            shards[d].push_back((uint32_t)i);
+            acc += job.len[i] + 72;
+        }
+    } else {
+        shard_lpt(job.len, job.n, ndev, shards);
+        // direct mode wants ascending addresses; LPT order is by size.  Re-sort each shard by the
+        // caller's order (for files that is listing order, which is also friendliest to the page cache).
+        for (auto &v : shards) std::sort(v.begin(), v.end());
+    }
     std::vector<int> rcs(ndev, 0);
     std::vector<std::string> errs(ndev);
     std::vector<std::thread> th;

@@ -1,0 +1,32 @@
+#!/usr/bin/env python3
+"""Ad-hoc: ONE process, one context over all visible GPUs (what a cgo caller has): C2-shaped units in one
+pinned host buffer, tpimd5_hash_buffers end to end."""
+import json, os, sys, time
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import oracle
+import tpi_b200 as tpi
+ndev = tpi.device_count()
+n, flen = (1 << 20) * min(ndev, 4), 4096
+host = torch.empty(n * flen, dtype=torch.uint8, pin_memory=True)
+hn = host.numpy()
+hn[:] = 0
+hn[: 1 << 26] = np.random.default_rng(1).integers(0, 256, 1 << 26, dtype=np.uint8)
+off = np.arange(n, dtype=np.uint64) * flen
+ln = np.full(n, flen, dtype=np.uint64)
+out = np.empty((n, 16), np.uint8)
+for devs in sorted({1, 2, 4, ndev}):
+    if devs > ndev:
+        continue
+    with tpi.Context(list(range(devs))) as c:
+        for _ in range(2):
+            c.hash_buffers(hn, off, ln, out=out)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            c.hash_buffers(hn, off, ln, out=out)
+        dt = (time.perf_counter() - t0) / 3
+    sel = [0, 1, n // 2, n - 1]
+    want = oracle.md5_batch(hn, off[sel], ln[sel])
+    assert np.array_equal(out[sel], want)
+    print(json.dumps({"devices_in_one_context": devs, "GiB": n * flen / 2**30, "ms": round(dt * 1e3, 1), "GBps": round(n * flen / dt / 1e9, 1)}))
