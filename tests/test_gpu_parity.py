@@ -543,3 +543,14 @@ def test_streams_mixed_write_paths_randomised(ctx):
     for s, r in zip(streams, ref):
         assert s.sum() == r.digest()
         s.close()
+
+
+def test_fuzz_host_api_short():
+    """Ten seconds of tools/fuzz_host_api.py (random layouts, alignments, staging sizes, pinned/pageable,
+    files) against the oracle.  Longer runs: `python tools/fuzz_host_api.py 300 <seed>`."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "fuzz_host_api.py"), "10", "777"], capture_output=True, text=True,
+                       timeout=300)
+    assert r.returncode == 0 and "fuzz ok" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
