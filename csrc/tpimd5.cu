@@ -142,7 +142,8 @@ class Pool {
 // ------------------------------------------------------------------------------------------------
 // context
 // ------------------------------------------------------------------------------------------------
-constexpr int NBUF = 4;                       // staging buffers (and batch kernels) in flight per device
+constexpr int NBUF = 8;                       // staging buffers (and batch kernels) in flight per device, allocated as needed:
+                                              // bytes in flight / time of the longest chain bounds ingest of large files
 constexpr size_t MAX_BATCH_LANES = 1u << 20;  // descriptor rows per staging buffer
 constexpr size_t DEFAULT_STAGING = 256u << 20;
 constexpr uint64_t MAX_LANE_BYTES = (uint64_t)60 << 30;  // one unit's bytes per launch (32-bit granule count)
@@ -160,7 +161,6 @@ struct Slot {
                                       // what keeps many chains in flight when single units take tens of ms
     // ingest staging (allocated on first use)
     size_t stage_bytes = 0;
-    bool staged = false;
     uint8_t *h_stage[NBUF] = {}, *d_stage[NBUF] = {};
     uint8_t *h_desc_raw[NBUF] = {}, *d_desc_raw[NBUF] = {};
     cudaEvent_t ev_copied[NBUF] = {}, ev_done[NBUF] = {};
@@ -214,18 +214,18 @@ static int ensure_scratch(Slot &s, size_t bytes) {
     return 0;
 }
 
-static int ensure_staging(tpimd5_ctx *ctx, Slot &s) {
-    if (s.staged) return 0;
-    s.stage_bytes = ctx->staging;
-    for (int i = 0; i < NBUF; ++i) {
-        CU(cudaHostAlloc(&s.h_stage[i], s.stage_bytes + 256, cudaHostAllocDefault));
+// Staging buffer i of a slot: device side, descriptors and events on first use; the pinned host side only
+// when something has to be packed (direct copies out of pinned caller memory never need it).
+static int ensure_buffer(tpimd5_ctx *ctx, Slot &s, int i, bool need_host) {
+    if (!s.stage_bytes) s.stage_bytes = ctx->staging;
+    if (!s.d_stage[i]) {
         CU(cudaMalloc(&s.d_stage[i], s.stage_bytes + 256));
         CU(cudaHostAlloc(&s.h_desc_raw[i], MAX_BATCH_LANES * desc_bytes_per_lane, cudaHostAllocDefault));
         CU(cudaMalloc(&s.d_desc_raw[i], MAX_BATCH_LANES * desc_bytes_per_lane));
         CU(cudaEventCreateWithFlags(&s.ev_copied[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&s.ev_done[i], cudaEventDisableTiming));
     }
-    s.staged = true;
+    if (need_host && !s.h_stage[i]) CU(cudaHostAlloc(&s.h_stage[i], s.stage_bytes + 256, cudaHostAllocDefault));
     return 0;
 }
 
@@ -762,9 +762,8 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
     }
     const std::vector<uint32_t> &units = job.paths ? by_size : units_in;
     CU(cudaSetDevice(s.dev));
-    int rc = ensure_staging(ctx, s);
-    if (rc) return rc;
-    rc = ensure_table(s, units.size());
+    s.stage_bytes = ctx->staging;
+    int rc = ensure_table(s, units.size());
     if (rc) return rc;
     const size_t nu = units.size();
     const bool from_files = job.paths != nullptr;
@@ -812,6 +811,8 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
 
     while (ui < nu) {
         const int bi = batch % NBUF;
+        rc = ensure_buffer(ctx, s, bi, !direct);
+        if (rc) return rc;
         // ---- plan one batch --------------------------------------------------------------------
         pieces.clear();
         uint64_t used = 0;       // bytes of staging consumed
