@@ -864,28 +864,35 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
         carve_desc(s.d_desc_raw[bi], np, dv);
         bool aligned = true;
         for (size_t i = 0; i < np; ++i) {
-            const Piece &p = pieces[order[i]];
-            const uint32_t u = units[p.unit];
-            h.off[i] = p.dst;
-            h.len[i] = p.len;
-            const uint64_t pr = (job.prior ? job.prior[u] : 0) + p.src_off;
-            h.prior[i] = pr;
-            const bool cont = p.src_off > 0 || job.init_states != nullptr;
-            const bool fin = p.last && !(job.nonfinal && job.nonfinal[u]);
-            h.flags[i] = (fin ? LANE_FINAL : 0u) | (cont ? LANE_CONT : 0u);
-            h.oidx[i] = p.unit;
-            aligned = aligned && (p.dst & 15) == 0;
-            if (p.len > MAX_LANE_BYTES) return fail(TPIMD5_ERANGE, "staging above %llu bytes per unit is not supported", (unsigned long long)MAX_LANE_BYTES);
+            aligned = aligned && (pieces[i].dst & 15) == 0;
+            if (pieces[i].len > MAX_LANE_BYTES) return fail(TPIMD5_ERANGE, "staging above %llu bytes per unit is not supported", (unsigned long long)MAX_LANE_BYTES);
         }
+        // descriptor rows [i0, i1) of this batch; run on the pool next to the packing, or, in direct mode,
+        // by this thread while the data copy is already under way
+        auto fill_desc = [&](size_t i0, size_t i1) {
+            for (size_t i = i0; i < i1; ++i) {
+                const Piece &p = pieces[order[i]];
+                const uint32_t u = units[p.unit];
+                h.off[i] = p.dst;
+                h.len[i] = p.len;
+                h.prior[i] = (job.prior ? job.prior[u] : 0) + p.src_off;
+                const bool cont = p.src_off > 0 || job.init_states != nullptr;
+                const bool fin = p.last && !(job.nonfinal && job.nonfinal[u]);
+                h.flags[i] = (fin ? LANE_FINAL : 0u) | (cont ? LANE_CONT : 0u);
+                h.oidx[i] = p.unit;
+            }
+        };
 
         // ---- bring the bytes to the device -----------------------------------------------------
         if (direct) {
             if (used > shift) CU(cudaMemcpyAsync(s.d_stage[bi] + shift, job.base + lo, used - shift, cudaMemcpyHostToDevice, s.s_copy));
+            fill_desc(0, np);
         } else {
             uint8_t *stage = s.h_stage[bi];
             // Work items are byte ranges, not units: a large file is read by several workers at once
             // (pread at different offsets), a run of tiny ones by a single worker.
             struct Task { uint32_t first, count; uint64_t lo, hi; };      // pieces [first, first+count); byte range of a lone piece
+                                                                          // (count 0: descriptor rows [lo, hi) instead)
             constexpr uint64_t CHUNK = 2u << 20;
             std::vector<Task> tasks;
             for (size_t i = 0; i < np;) {
@@ -905,8 +912,10 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
                 int expect = 0;
                 if (io_err.compare_exchange_strong(expect, r == -1 ? (errno ? errno : EIO) : r)) io_idx = u;
             };
+            for (size_t i0 = 0; i0 < np; i0 += 8192) tasks.push_back({0, 0, i0, std::min<uint64_t>(np, i0 + 8192)});
             std::function<void(size_t)> fill = [&](size_t t) {
                 const Task &tk = tasks[t];
+                if (tk.count == 0) { fill_desc((size_t)tk.lo, (size_t)tk.hi); return; }
                 for (uint32_t i = tk.first; i < tk.first + tk.count; ++i) {
                     const Piece &p = pieces[i];
                     const uint32_t u = units[p.unit];
