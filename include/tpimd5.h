@@ -183,7 +183,13 @@ TPIMD5_API int tpimd5_transfer_local(tpimd5_ctx *ctx, const char *source, const 
  * The calls only enqueue work.  These are what kernel-only throughput is measured through;
  * the reference has no counterpart (its data is never on a device).
  *   offsets == NULL: unit i is bytes [i*stride, min((i+1)*stride, base_bytes)) (fixed-size
- *   files / S3 parts), with lengths ignored. */
+ *   files / S3 parts), with lengths ignored; a 16-byte aligned base and stride take the
+ *   TMA-fed kernel.
+ *   Scratch: hash_buffers with offset arrays (>= 4,096 units are bucketed by length with a
+ *   device radix sort), s3_etag with d_part_digests == NULL, and diff (tile counts) keep their
+ *   temporaries in one per-slot buffer that grows on demand (cudaMalloc on first use).  Calls
+ *   that use it on the same slot must not overlap on the GPU: keep them on one stream, or pass
+ *   your own part-digest buffer, or use one slot (device) per stream. */
 TPIMD5_API int tpimd5_dev_hash_buffers(tpimd5_ctx *ctx, int slot, const void *d_base, uint64_t base_bytes,
                             const uint64_t *d_offsets, const uint64_t *d_lengths, uint64_t stride, size_t n,
                             void *d_digests_out, void *cuda_stream);
