@@ -20,7 +20,11 @@
 #include <cstring>
 #include <dirent.h>
 #include <string>
+#include <condition_variable>
+#include <fcntl.h>
+#include <mutex>
 #include <sys/stat.h>
+#include <thread>
 #include <vector>
 
 extern "C" void tpimd5_set_error_(const char *msg);   // defined in tpimd5.cu
@@ -195,27 +199,75 @@ bool is_rclone_filter(const std::string &r) { return r.rfind("+ ", 0) == 0 || r.
 }  // namespace
 
 struct tpimd5_filter {
-    std::vector<Rule> rules;
+    std::vector<std::string> texts;   // every rule as added, normalised ("+ glob" / "- glob")
+    std::vector<Rule> rules;          // file rules: first match decides whether a file is in
+    std::vector<Rule> dir_rules;      // directory rules, matched against "path/to/dir/": whether to descend
 };
 
-static bool add_rule(tpimd5_filter &f, std::string rule, std::string &err) {
-    if (!is_rclone_filter(rule)) rule = "- " + join_root(rule);            // storage.go:131-134
-    Rule r;
-    r.include = rule[0] == '+';
-    r.text = rule;
-    std::string glob = rule.substr(2);
-    while (!glob.empty() && glob[0] == ' ') glob.erase(0, 1);
-    while (!glob.empty() && glob.back() == ' ') glob.pop_back();
-    if (glob.empty()) { err = "empty filter rule"; return false; }
-    if (glob.back() == '/') glob += "**";                                   // directory rule: everything beneath
+static bool compile_alts(const std::string &glob, std::vector<Pattern> &out, std::string &err) {
     std::vector<std::string> alts;
     if (!expand_braces(glob, alts, err)) return false;
     for (const auto &a : alts) {
         Pattern p;
         if (!compile_glob(a, p, err)) return false;
-        r.pats.push_back(std::move(p));
+        out.push_back(std::move(p));
     }
-    f.rules.push_back(std::move(r));
+    return true;
+}
+
+// [rclone] fs/filter globToDirGlobs: the directories a file glob could have matches in, as globs to be
+// matched against a directory path with a trailing slash.  "/a/b/**" -> "/a/b/**/", "/a/b/", "/a/", "/";
+// a glob without any slash could match anywhere -> "/**".
+static std::vector<std::string> glob_to_dir_globs(std::string glob) {
+    std::vector<std::string> out;
+    for (;;) {
+        const size_t si = glob.rfind('/'), sj = glob.rfind("**");
+        long i = si == std::string::npos ? -1 : (long)si;
+        const long j = sj == std::string::npos ? -1 : (long)sj;
+        std::string what;
+        if (j > i) { i = j; what = "**"; }
+        if (i < 0) {
+            if (out.empty()) out.push_back("/**");
+            break;
+        }
+        glob = glob.substr(0, (size_t)i);
+        const std::string g = glob + what + "/";
+        if (out.empty() || out.back() != g) out.push_back(g);
+    }
+    return out;
+}
+
+// [rclone] fs/filter Filter.Add: a glob ending in "/" is a directory rule (an excluded "dir/" means
+// "dir/**"); a glob containing "**" is both a file and a directory rule; an include file rule also
+// includes the directories that lead to it (an exclude rule cannot rule a directory out, except "*").
+static bool add_rule(tpimd5_filter &f, std::string rule, std::string &err) {
+    if (!is_rclone_filter(rule)) rule = "- " + join_root(rule);            // storage.go:131-134
+    const bool include = rule[0] == '+';
+    std::string glob = rule.substr(2);
+    while (!glob.empty() && glob[0] == ' ') glob.erase(0, 1);
+    while (!glob.empty() && glob.back() == ' ') glob.pop_back();
+    if (glob.empty()) { err = "empty filter rule"; return false; }
+    bool is_dir = glob.back() == '/', is_file = !is_dir;
+    if (is_dir && !include) glob += "**";
+    if (glob.find("**") != std::string::npos) is_dir = is_file = true;
+    Rule r;
+    r.include = include;
+    r.text = rule;
+    if (!compile_alts(glob, r.pats, err)) return false;
+    f.texts.push_back(rule);
+    if (is_file) {
+        f.rules.push_back(r);
+        if (include || glob == "*") {
+            for (const std::string &dg : glob_to_dir_globs(glob)) {
+                Rule d;
+                d.include = include;
+                d.text = rule;
+                if (!compile_alts(dg, d.pats, err)) return false;
+                f.dir_rules.push_back(std::move(d));
+            }
+        }
+    }
+    if (is_dir) f.dir_rules.push_back(r);
     return true;
 }
 
@@ -246,9 +298,9 @@ extern "C" int tpimd5_filter_new(const char *const *exclude, size_t n_exclude, c
 }
 
 extern "C" void tpimd5_filter_free(tpimd5_filter *f) { delete f; }
-extern "C" size_t tpimd5_filter_rule_count(const tpimd5_filter *f) { return f ? f->rules.size() : 0; }
+extern "C" size_t tpimd5_filter_rule_count(const tpimd5_filter *f) { return f ? f->texts.size() : 0; }
 extern "C" const char *tpimd5_filter_rule(const tpimd5_filter *f, size_t i) {
-    return (f && i < f->rules.size()) ? f->rules[i].text.c_str() : nullptr;
+    return (f && i < f->texts.size()) ? f->texts[i].c_str() : nullptr;
 }
 
 extern "C" int tpimd5_filter_include(const tpimd5_filter *f, const char *rel_path) {
@@ -258,6 +310,21 @@ extern "C" int tpimd5_filter_include(const tpimd5_filter *f, const char *rel_pat
     for (const Rule &r : f->rules)
         for (const Pattern &p : r.pats)
             if (pattern_matches(p, rel_path, n)) return r.include ? 1 : 0;
+    return 1;
+}
+
+// Would rclone descend into (and, with copyEmptySrcDirs, create) this directory?  rel_dir without or with
+// a trailing slash; the root is always in.
+extern "C" int tpimd5_filter_include_dir(const tpimd5_filter *f, const char *rel_dir) {
+    if (!f || !rel_dir) return fail(TPIMD5_EINVAL, "filter_include_dir: null pointer");
+    while (*rel_dir == '/') ++rel_dir;
+    std::string d(rel_dir);
+    while (!d.empty() && d.back() == '/') d.pop_back();
+    if (d.empty()) return 1;
+    d += '/';
+    for (const Rule &r : f->dir_rules)
+        for (const Pattern &p : r.pats)
+            if (pattern_matches(p, d.c_str(), d.size())) return r.include ? 1 : 0;
     return 1;
 }
 
@@ -280,38 +347,98 @@ static void sort_entries(tpimd5_manifest &m) {
     std::sort(m.e.begin(), m.e.end(), [](const Entry &a, const Entry &b) { return a.path < b.path; });
 }
 
-static int walk(const std::string &root, const std::string &rel, const tpimd5_filter *f, std::vector<Entry> &out) {
-    const std::string dir = rel.empty() ? root : root + "/" + rel;
-    DIR *d = opendir(dir.c_str());
-    if (!d) return fail(TPIMD5_EIO, dir + ": " + strerror(errno));
-    std::vector<std::string> subdirs;
-    for (;;) {
-        errno = 0;
-        struct dirent *de = readdir(d);
-        if (!de) break;
-        const char *nm = de->d_name;
-        if (!strcmp(nm, ".") || !strcmp(nm, "..")) continue;
-        const std::string r = rel.empty() ? std::string(nm) : rel + "/" + nm;
-        struct stat sb;
-        if (lstat((root + "/" + r).c_str(), &sb) != 0) { closedir(d); return fail(TPIMD5_EIO, root + "/" + r + ": " + strerror(errno)); }
-        if (S_ISDIR(sb.st_mode)) {
-            subdirs.push_back(r);
-        } else if (S_ISREG(sb.st_mode)) {                       // rclone's local backend skips symlinks and specials
-            if (f && tpimd5_filter_include(f, r.c_str()) != 1) continue;
-            Entry e;
-            e.path = r;
-            e.size = (uint64_t)sb.st_size;
-            e.mtime_ns = (int64_t)sb.st_mtim.tv_sec * 1000000000ll + sb.st_mtim.tv_nsec;
-            out.push_back(std::move(e));
+// Lists a local tree the way [rclone] backend/local + fs/walk do under a filter: regular files only
+// (symlinks and specials skipped), a directory is entered only if the directory rules allow it, a file is
+// kept only if the file rules do.  Directories are listed by a few threads at once: on a million small
+// files the lstat calls cost as much as the hashing.
+struct TreeLister {
+    std::string root;
+    const tpimd5_filter *f = nullptr;
+    std::mutex mu;
+    std::condition_variable cv;
+    std::vector<std::string> queue;      // directories (relative) waiting to be listed
+    size_t pending = 0;                  // queued + being listed
+    int err = 0;
+    std::string err_text;
+    std::vector<Entry> files;
+    std::vector<std::string> dirs;
+
+    void list_one(const std::string &rel, std::vector<Entry> &my_files, std::vector<std::string> &my_dirs, std::vector<std::string> &sub) {
+        const std::string dir = rel.empty() ? root : root + "/" + rel;
+        DIR *d = opendir(dir.c_str());
+        if (!d) { set_err(dir + ": " + strerror(errno)); return; }
+        for (;;) {
+            struct dirent *de = readdir(d);
+            if (!de) break;
+            const char *nm = de->d_name;
+            if (!strcmp(nm, ".") || !strcmp(nm, "..")) continue;
+            struct stat sb;
+            if (fstatat(dirfd(d), nm, &sb, AT_SYMLINK_NOFOLLOW) != 0) { set_err(dir + "/" + nm + ": " + strerror(errno)); break; }
+            std::string r = rel.empty() ? std::string(nm) : rel + "/" + nm;
+            if (S_ISDIR(sb.st_mode)) {
+                if (f && tpimd5_filter_include_dir(f, r.c_str()) != 1) continue;
+                my_dirs.push_back(r);
+                sub.push_back(std::move(r));
+            } else if (S_ISREG(sb.st_mode)) {
+                if (f && tpimd5_filter_include(f, r.c_str()) != 1) continue;
+                Entry e;
+                e.path = std::move(r);
+                e.size = (uint64_t)sb.st_size;
+                e.mtime_ns = (int64_t)sb.st_mtim.tv_sec * 1000000000ll + sb.st_mtim.tv_nsec;
+                my_files.push_back(std::move(e));
+            }
         }
+        closedir(d);
     }
-    closedir(d);
-    for (const auto &s : subdirs) {
-        int rc = walk(root, s, f, out);
-        if (rc) return rc;
+    void set_err(const std::string &t) {
+        std::lock_guard<std::mutex> g(mu);
+        if (!err) { err = TPIMD5_EIO; err_text = t; }
     }
-    return 0;
-}
+    void worker() {
+        std::vector<Entry> my_files;
+        std::vector<std::string> my_dirs, sub;
+        for (;;) {
+            std::string rel;
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] { return !queue.empty() || pending == 0; });
+                if (queue.empty()) break;
+                rel = std::move(queue.back());
+                queue.pop_back();
+            }
+            sub.clear();
+            list_one(rel, my_files, my_dirs, sub);
+            {
+                std::lock_guard<std::mutex> g(mu);
+                for (auto &x : sub) queue.push_back(std::move(x));
+                pending += sub.size();
+                --pending;
+            }
+            cv.notify_all();
+        }
+        std::lock_guard<std::mutex> g(mu);
+        for (auto &e : my_files) files.push_back(std::move(e));
+        for (auto &x : my_dirs) dirs.push_back(std::move(x));
+    }
+    int run(bool missing_ok) {
+        struct stat sb;
+        if (stat(root.c_str(), &sb) != 0) {
+            if (missing_ok && errno == ENOENT) return 0;
+            return fail(TPIMD5_EIO, root + ": " + strerror(errno));
+        }
+        queue.push_back("");
+        pending = 1;
+        unsigned hc = std::thread::hardware_concurrency();
+        const int nth = (int)std::min<unsigned>(hc ? hc : 4, 16);
+        std::vector<std::thread> th;
+        for (int t = 1; t < nth; ++t) th.emplace_back([this] { worker(); });
+        worker();
+        for (auto &t : th) t.join();
+        if (err) return fail(err, err_text);
+        std::sort(dirs.begin(), dirs.end());
+        return 0;
+    }
+};
 
 extern "C" int tpimd5_manifest_scan(tpimd5_ctx *ctx, const char *root, const tpimd5_filter *filter, tpimd5_manifest **out) {
     if (!ctx || !root || !out) return fail(TPIMD5_EINVAL, "manifest_scan: null pointer");
@@ -319,8 +446,12 @@ extern "C" int tpimd5_manifest_scan(tpimd5_ctx *ctx, const char *root, const tpi
     tpimd5_manifest *m = new tpimd5_manifest;
     std::string r(root);
     while (r.size() > 1 && r.back() == '/') r.pop_back();
-    int rc = walk(r, "", filter, m->e);
+    TreeLister lister;
+    lister.root = r;
+    lister.f = filter;
+    int rc = lister.run(false);
     if (rc) { delete m; return rc; }
+    m->e = std::move(lister.files);
     sort_entries(*m);
     const size_t n = m->e.size();
     if (n) {
@@ -527,49 +658,6 @@ extern "C" int tpimd5_plan_transfer(tpimd5_ctx *ctx, const tpimd5_manifest *src,
 
 namespace {
 
-struct Listing {
-    std::vector<Entry> files;
-    std::vector<std::string> dirs;
-};
-
-int list_tree(const std::string &root, const std::string &rel, const tpimd5_filter *f, Listing &out, bool missing_ok) {
-    const std::string dir = rel.empty() ? root : root + "/" + rel;
-    DIR *d = opendir(dir.c_str());
-    if (!d) {
-        if (missing_ok && errno == ENOENT && rel.empty()) return 0;
-        return fail(TPIMD5_EIO, dir + ": " + strerror(errno));
-    }
-    std::vector<std::string> subdirs;
-    for (;;) {
-        struct dirent *de = readdir(d);
-        if (!de) break;
-        const char *nm = de->d_name;
-        if (!strcmp(nm, ".") || !strcmp(nm, "..")) continue;
-        const std::string r = rel.empty() ? std::string(nm) : rel + "/" + nm;
-        struct stat sb;
-        if (lstat((root + "/" + r).c_str(), &sb) != 0) { closedir(d); return fail(TPIMD5_EIO, root + "/" + r + ": " + strerror(errno)); }
-        if (S_ISDIR(sb.st_mode)) {
-            // a directory is entered unless a rule rejects everything that could be inside it
-            if (f && tpimd5_filter_include(f, (r + "/").c_str()) != 1) continue;
-            subdirs.push_back(r);
-        } else if (S_ISREG(sb.st_mode)) {
-            if (f && tpimd5_filter_include(f, r.c_str()) != 1) continue;
-            Entry e;
-            e.path = r;
-            e.size = (uint64_t)sb.st_size;
-            e.mtime_ns = (int64_t)sb.st_mtim.tv_sec * 1000000000ll + sb.st_mtim.tv_nsec;
-            out.files.push_back(std::move(e));
-        }
-    }
-    closedir(d);
-    for (const auto &s : subdirs) {
-        out.dirs.push_back(s);
-        int rc = list_tree(root, s, f, out, false);
-        if (rc) return rc;
-    }
-    return 0;
-}
-
 int mkdir_p(const std::string &path) {
     std::string cur;
     for (size_t i = 0; i <= path.size(); ++i) {
@@ -629,9 +717,11 @@ extern "C" int tpimd5_transfer_local(tpimd5_ctx *ctx, const char *source, const 
     int rc = tpimd5_filter_new(exclude, n_exclude, limit_subdir, &flt);
     if (rc) return rc;
     const std::string src = strip_slashes(source), dst = strip_slashes(destination);
-    Listing ls, ld;
-    rc = list_tree(src, "", flt, ls, false);
-    if (!rc) rc = list_tree(dst, "", flt, ld, true);
+    TreeLister ls, ld;
+    ls.root = src; ls.f = flt;
+    ld.root = dst; ld.f = flt;
+    rc = ls.run(false);
+    if (!rc) rc = ld.run(true);
     tpimd5_filter_free(flt);
     if (rc) return rc;
     tpimd5_manifest ms, md;

@@ -121,7 +121,10 @@ TPIMD5_API int tpimd5_diff(tpimd5_ctx *ctx, const uint8_t *old16, const uint8_t 
  * "- " + filepath.Join("/", rule)) and, when limit_subdir is non-NULL, LimitTransfer
  * (storage.go:267-280: include that directory and everything beneath it, exclude the rest), with [rclone] fs/filter glob semantics
  * (first matching rule wins, no match = include; a glob with a leading "/" matches from the root,
- * any other glob after any "/"; "*" stays within a path segment, "**" does not).  Pinned by the
+ * any other glob after any "/"; "*" stays within a path segment, "**" does not).  Directories
+ * follow rclone's derived directory rules (_include_dir): a glob with "**" or a trailing "/" is a
+ * directory rule too, an include rule also includes the directories leading to it, so a nested
+ * DirectoryOut (include rules for a/b placed before the final exclude-everything) is still reached.  Pinned by the
  * expectations of storage_test.go:55-101.  Pure host code: works without a GPU.
  *
  * tpimd5_manifest_*: {relative path, size, mtime_ns, md5} per object, sorted by path.  The
@@ -145,6 +148,7 @@ typedef struct tpimd5_manifest tpimd5_manifest;
 TPIMD5_API int tpimd5_filter_new(const char *const *exclude, size_t n_exclude, const char *limit_subdir, tpimd5_filter **out);
 TPIMD5_API void tpimd5_filter_free(tpimd5_filter *f);
 TPIMD5_API int tpimd5_filter_include(const tpimd5_filter *f, const char *rel_path);
+TPIMD5_API int tpimd5_filter_include_dir(const tpimd5_filter *f, const char *rel_dir);
 TPIMD5_API size_t tpimd5_filter_rule_count(const tpimd5_filter *f);
 TPIMD5_API const char *tpimd5_filter_rule(const tpimd5_filter *f, size_t i);
 TPIMD5_API int tpimd5_manifest_scan(tpimd5_ctx *ctx, const char *root, const tpimd5_filter *filter, tpimd5_manifest **out);

@@ -320,19 +320,52 @@ def glob_to_regex(glob: str) -> str:
     return "".join(out)
 
 
+def glob_to_dir_globs(glob: str) -> List[str]:
+    """rclone fs/filter globToDirGlobs: directories a file glob could match in (as globs for "dir/")."""
+    out: List[str] = []
+    while True:
+        i, j = glob.rfind("/"), glob.rfind("**")
+        what = ""
+        if j > i:
+            i, what = j, "**"
+        if i < 0:
+            if not out:
+                out.append("/**")
+            break
+        glob = glob[:i]
+        g = glob + what + "/"
+        if not out or out[-1] != g:
+            out.append(g)
+    return out
+
+
 class FilterSet:
-    """First matching rule wins; no match => included (rclone filter semantics for files)."""
+    """rclone filter semantics (fs/filter Filter.Add / Include / IncludeDirectory): the first matching
+    file rule decides for a file, no match => included; directories are decided by the derived
+    directory rules, matched against "dir/"."""
 
     def __init__(self, rules: Iterable[str]):
         self.rules = []
+        self.dir_rules = []
         for r in rules:
             if not is_rclone_filter(r):
                 raise ValueError(f"not an rclone filter rule: {r!r}")
             include = r[0] == "+"
             g = r[2:].strip()
-            if g.endswith("/"):          # directory rule: everything underneath
+            is_dir = g.endswith("/")
+            is_file = not is_dir
+            if is_dir and not include:          # excluding "dir/" means "dir/**"
                 g += "**"
-            self.rules.append((include, re.compile(glob_to_regex(g))))
+            if "**" in g:
+                is_dir = is_file = True
+            rx = re.compile(glob_to_regex(g))
+            if is_file:
+                self.rules.append((include, rx))
+                if include or g == "*":
+                    for dg in glob_to_dir_globs(g):
+                        self.dir_rules.append((include, re.compile(glob_to_regex(dg))))
+            if is_dir:
+                self.dir_rules.append((include, rx))
 
     def include_file(self, rel_path: str) -> bool:
         rel_path = rel_path.lstrip("/")
@@ -341,8 +374,26 @@ class FilterSet:
                 return inc
         return True
 
+    def include_dir(self, rel_dir: str) -> bool:
+        d = rel_dir.strip("/")
+        if not d:
+            return True
+        d += "/"
+        for inc, rx in self.dir_rules:
+            if rx.search(d):
+                return inc
+        return True
+
+    def include_path(self, rel_path: str) -> bool:
+        """A file as a filtered WALK sees it: every directory on the way must be entered."""
+        parts = rel_path.strip("/").split("/")
+        for k in range(1, len(parts)):
+            if not self.include_dir("/".join(parts[:k])):
+                return False
+        return self.include_file(rel_path)
+
 
 def list_transfer(files: Iterable[str], exclude: Optional[Iterable[str]] = None) -> List[str]:
     """The relative paths machine.Transfer would move, given the source file listing."""
     fs = FilterSet(transfer_rules(exclude))
-    return sorted(f for f in files if fs.include_file(f))
+    return sorted(f for f in files if fs.include_path(f))

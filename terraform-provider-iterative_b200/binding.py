@@ -22,7 +22,7 @@ EXPORTS = [
     "tpimd5_s3_etag_buffer", "tpimd5_s3_etag_file", "tpimd5_stream_open", "tpimd5_stream_write",
     "tpimd5_stream_write_many", "tpimd5_stream_sum", "tpimd5_stream_reset", "tpimd5_stream_close", "tpimd5_diff",
     "tpimd5_dev_hash_buffers", "tpimd5_dev_s3_etag", "tpimd5_dev_diff", "tpimd5_dev_synth_fill",
-    "tpimd5_dev_s3_etag_noalloc", "tpimd5_filter_new", "tpimd5_filter_free", "tpimd5_filter_include",
+    "tpimd5_dev_s3_etag_noalloc", "tpimd5_filter_new", "tpimd5_filter_free", "tpimd5_filter_include", "tpimd5_filter_include_dir",
     "tpimd5_filter_rule_count", "tpimd5_filter_rule", "tpimd5_manifest_scan", "tpimd5_manifest_from_arrays",
     "tpimd5_manifest_free", "tpimd5_manifest_count", "tpimd5_manifest_entry", "tpimd5_manifest_save",
     "tpimd5_manifest_load", "tpimd5_manifest_write_md5sum", "tpimd5_plan_transfer", "tpimd5_transfer_local",
@@ -80,6 +80,7 @@ def load_library() -> C.CDLL:
         "tpimd5_filter_new": (i32, [vp, sz, C.c_char_p, C.POINTER(vp)]),
         "tpimd5_filter_free": (None, [vp]),
         "tpimd5_filter_include": (i32, [vp, C.c_char_p]),
+        "tpimd5_filter_include_dir": (i32, [vp, C.c_char_p]),
         "tpimd5_filter_rule_count": (sz, [vp]),
         "tpimd5_filter_rule": (C.c_char_p, [vp, sz]),
         "tpimd5_manifest_scan": (i32, [vp, C.c_char_p, vp, C.POINTER(vp)]),

@@ -35,6 +35,13 @@ class Filter:
             _check(r)
         return r == 1
 
+    def include_dir(self, rel_dir: str) -> bool:
+        """Would rclone descend into (and create) this directory under these rules?"""
+        r = self._L.tpimd5_filter_include_dir(self._h, os.fsencode(rel_dir))
+        if r < 0:
+            _check(r)
+        return r == 1
+
     def rules(self) -> List[str]:
         n = self._L.tpimd5_filter_rule_count(self._h)
         return [self._L.tpimd5_filter_rule(self._h, i).decode() for i in range(n)]

@@ -75,7 +75,7 @@ def test_manifest_scan_is_the_filtered_listing_with_oracle_digests(ctx, tmp_path
     flt = tpi.Filter(["cache", "**.txt"])
     m = tpi.Manifest.scan(ctx, root, flt)
     o = oracle.FilterSet(oracle.transfer_rules(["cache", "**.txt"]))
-    want = sorted(p for p in files if o.include_file(p))
+    want = sorted(p for p in files if o.include_path(p))
     assert m.paths() == want and "link" not in m.paths()
     for p, size, mtime, md5 in m.entries():
         assert size == len(files[p]) and md5 == oracle.md5(files[p])
@@ -132,7 +132,7 @@ def test_transfer_then_resync_with_checksum_finds_exactly_the_changed_files(ctx,
     files = build_workdir(src, 63, n=80)
     st = machine.Transfer(ctx, src, dst, ["cache"])
     o = oracle.FilterSet(oracle.transfer_rules(["cache"]))
-    moved = sorted(p for p in files if o.include_file(p))
+    moved = sorted(p for p in files if o.include_path(p))
     assert st["transferred"] == len(moved) == st["files_listed"] and st["bytes_listed"] == sum(len(files[p]) for p in moved)
     for p in moved:
         assert open(os.path.join(dst, p), "rb").read() == files[p]
@@ -174,6 +174,20 @@ def test_pull_limited_to_the_output_directory(ctx, tmp_path):
     assert not os.path.exists(os.path.join(dst, "cache")) and not os.path.exists(os.path.join(dst, "data"))
 
 
+def test_pull_limited_to_a_nested_output_directory(ctx, tmp_path):
+    """DirectoryOut may be nested: "+ /data/deep", "+ /data/deep/**", "- /**".  rclone still descends through
+    data/ (directory rules derived from the include rules) but brings back nothing else from it."""
+    src, dst = str(tmp_path / "bucket-data"), str(tmp_path / "workdir")
+    files = build_workdir(src, 66, n=120)
+    machine.Transfer(ctx, src, dst, machine.LimitTransfer("data/deep", []))
+    got = [p[1:] for p in list_dir(dst) if os.path.isfile(os.path.join(dst, p[1:]))]
+    want = sorted(p for p in files if p.startswith("data/deep/"))
+    assert got == want and got
+    assert sorted(os.listdir(dst)) == ["data"] and sorted(os.listdir(os.path.join(dst, "data"))) == ["deep"]
+    o = oracle.FilterSet(oracle.limit_transfer("data/deep", oracle.transfer_rules([])))
+    assert want == sorted(p for p in files if o.include_path(p))
+
+
 def test_transfer_refuses_cloud_remotes(ctx, tmp_path):
     with pytest.raises(tpi.TpiMd5Error):
         machine.Transfer(ctx, str(tmp_path), ":s3,provider=AWS:bucket/data")
@@ -195,7 +209,7 @@ def test_cli_prints_what_md5sum_prints_and_detects_changes(tmp_path):
     man = str(tmp_path / "old.tpim")
     out = subprocess.run([CLI, "--manifest", root, "-x", "**.txt", "-o", man], capture_output=True, text=True)
     o = oracle.FilterSet(oracle.transfer_rules(["**.txt"]))
-    keep = sorted(p for p in files if o.include_file(p))
+    keep = sorted(p for p in files if o.include_path(p))
     assert out.returncode == 0 and out.stdout == "".join(oracle.md5sum_line(oracle.md5(files[p]), p) for p in keep)
     # nothing changed -> exit 0 and no lines
     r = subprocess.run([CLI, "--changed", man, root, "-x", "**.txt"], capture_output=True, text=True)

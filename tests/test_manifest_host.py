@@ -124,3 +124,30 @@ def test_plan_refuses_to_compare_digests_without_a_gpu():
     with pytest.raises(tpi.TpiMd5Error) as e:
         tpi.plan_transfer(None, src, dst, tpi.manifest.MODE_CHECKSUM)
     assert e.value.code == -2 and "no CPU fallback" in str(e.value)
+
+
+def test_directory_rules_against_oracle_randomised():
+    """rclone decides directories by rules derived from the file rules (globs with "**", trailing "/",
+    parents of include rules).  The C++ filter and the oracle's restatement must agree on every
+    directory, and a nested DirectoryOut must stay reachable."""
+    rnd = random.Random(58)
+    segs = ["a", "b", "data", "out", "deep", ".terraform", "x.d", "1"]
+    dirs = ["/".join(rnd.choice(segs) for _ in range(rnd.randint(1, 4))) for _ in range(300)]
+    globs = ["*.txt", "**.txt", "/a/**", "a/*", "/*/b", "data/", "/out/", "out/deep/**", "/a/b/c.bin", "*", "**", "/**", "x.d/**",
+             "{a,b}/**", "/data/deep/", "b/1"]
+    for _ in range(80):
+        rules = [rnd.choice(["+ ", "- ", ""]) + rnd.choice(globs) for _ in range(rnd.randint(0, 4))]
+        limit = rnd.choice([None, "out", "data/deep", "a/b/1"])
+        f = tpi.Filter(rules, limit)
+        o_rules = oracle.transfer_rules(rules)
+        if limit:
+            o_rules = oracle.limit_transfer(limit, o_rules)
+        o = oracle.FilterSet(o_rules)
+        for d in dirs:
+            assert f.include_dir(d) == o.include_dir(d), (rules, limit, d)
+    f = tpi.Filter(["cache"], "data/deep")                    # Pull with a nested output directory
+    assert f.include_dir("data") and f.include_dir("data/deep") and f.include_dir("data/deep/er")
+    assert not f.include_dir("cache") and not f.include_dir("data/other") and not f.include_dir("out")
+    assert f.include("data/deep/file") and not f.include("data/file")
+    f = tpi.Filter([])                                        # built-ins: "/.terraform**" prunes the directory itself
+    assert not f.include_dir(".terraform") and not f.include_dir(".terraform/providers") and f.include_dir("src/.terraform")
