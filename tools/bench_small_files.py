@@ -34,6 +34,10 @@ try:
             t0 = time.perf_counter()
             got = c.hash_files(paths, sizes)
             t.append(time.perf_counter() - t0)
+        t0 = time.perf_counter()
+        m = tpi.Manifest.scan(c, root, tpi.Filter([]))
+        t_scan = time.perf_counter() - t0
+        assert len(m) == n
     eng = oracle.ENGINE_OPENSSL if oracle.lib().orc_has_openssl() else 0
     oracle.md5_files(paths[:1000], 4, eng)
     t0 = time.perf_counter()
@@ -41,6 +45,6 @@ try:
     tc = time.perf_counter() - t0
     assert np.array_equal(got, want)
     print(json.dumps({"files": n, "gpu_path_s": round(min(t), 3), "gpu_files_per_s": round(n / min(t)), "gpu_GBps": round(n * 4096 / min(t) / 1e9, 3),
-                      "cpu_s": round(tc, 3), "cpu_files_per_s": round(n / tc), "cpu_GBps": round(n * 4096 / tc / 1e9, 3), "cpu_threads": os.cpu_count()}))
+                      "manifest_scan_s": round(t_scan, 3), "cpu_s": round(tc, 3), "cpu_files_per_s": round(n / tc), "cpu_GBps": round(n * 4096 / tc / 1e9, 3), "cpu_threads": os.cpu_count()}))
 finally:
     shutil.rmtree(root, ignore_errors=True)
