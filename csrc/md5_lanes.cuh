@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) md5_lanes_kernel(const LaneA
     extern __shared__ __align__(128) uint8_t smem_raw[];
 
     const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // provably warp-uniform: stays in uniform registers
     const uint64_t u = (uint64_t)blockIdx.x * (WARPS * 32) + threadIdx.x;
     const bool valid = u < p.n;
 

@@ -49,7 +49,10 @@ md5_strided_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uin
     constexpr uint32_t SB = 128u * TILES;                     // bytes of one unit per stage
     constexpr uint32_t BPS = 2u * TILES;                      // MD5 blocks per stage
     extern __shared__ uint8_t smem_raw[];
-    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t lane = threadIdx.x & 31u;
+    // broadcast from lane 0 so that the compiler knows the warp index (and all that follows from it: tile
+    // and mbarrier addresses, TMA coordinates) is warp-uniform and keeps it in uniform registers
+    const uint32_t warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
     const uint64_t u0 = ((uint64_t)blockIdx.x * WARPS + warp) * 32u;         // first unit of this warp
     if (u0 >= n) return;                                                      // warp-uniform
     const uint64_t u = u0 + lane;
