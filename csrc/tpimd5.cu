@@ -146,7 +146,7 @@ constexpr int NBUF = 8;                       // staging buffers (and batch kern
                                               // bytes in flight / time of the longest chain bounds ingest of large files
 constexpr size_t MAX_BATCH_LANES = 1u << 20;  // descriptor rows per staging buffer
 constexpr size_t DEFAULT_STAGING = 256u << 20;
-constexpr uint64_t MAX_LANE_BYTES = (uint64_t)60 << 30;  // one unit's bytes per launch (32-bit granule count)
+constexpr uint64_t MAX_LANE_BYTES = (uint64_t)31 << 30;  // one unit's bytes per launch (the kernels count its 16-byte granules in an int32)
 
 struct LaneDesc {  // device / pinned mirrors, structure of arrays
     uint64_t *off = nullptr, *len = nullptr, *prior = nullptr;
