@@ -167,3 +167,16 @@ def test_filter_details():
     assert fs.include_file("out/file") and fs.include_file("out/deep/er")
     assert not fs.include_file("cache/file") and not fs.include_file("other")
     assert oracle.limit_transfer(".", ["- /x"]) == ["- /x"]
+
+
+def test_dir_globs_derivation():
+    """The directory globs rclone derives from a file glob (fs/filter globToDirGlobs), on worked examples."""
+    g = oracle.glob_to_dir_globs
+    assert g("/a/b/**") == ["/a/b/**/", "/a/b/", "/a/", "/"]
+    assert g("/out") == ["/"]
+    assert g("/a/b/c.txt") == ["/a/b/", "/a/", "/"]
+    assert g("x.txt") == ["/**"]                       # could be anywhere: every directory stays in
+    assert g("a/b.txt") == ["a/"]
+    fs = oracle.FilterSet(oracle.limit_transfer("a/b", oracle.transfer_rules([])))
+    assert fs.include_dir("a") and fs.include_dir("a/b") and fs.include_dir("a/b/c") and not fs.include_dir("z")
+    assert fs.include_path("a/b/f") and not fs.include_path("a/f") and not fs.include_path("z/a/b/f")
