@@ -145,7 +145,7 @@ class Pool {
 constexpr int NBUF = 8;                       // staging buffers (and batch kernels) in flight per device, allocated as needed:
                                               // bytes in flight / time of the longest chain bounds ingest of large files
 constexpr size_t MAX_BATCH_LANES = 1u << 20;  // descriptor rows per staging buffer
-constexpr size_t DEFAULT_STAGING = 256u << 20;
+constexpr size_t DEFAULT_STAGING = 256u << 20;   // measured best for C1/C2 end to end; 512 MiB is better for multi-GiB files (see tpimd5_init)
 constexpr uint64_t MAX_LANE_BYTES = (uint64_t)31 << 30;  // one unit's bytes per launch (the kernels count its 16-byte granules in an int32)
 
 struct LaneDesc {  // device / pinned mirrors, structure of arrays
