@@ -21,8 +21,9 @@ try:
     paths = []
     for d in range(1024):
         os.makedirs(os.path.join(root, f"{d:04d}"))
+    per_dir = (n + 1023) // 1024
     for i in range(n):
-        p = os.path.join(root, f"{i % 1024:04d}", f"{i:07d}")
+        p = os.path.join(root, f"{i // per_dir:04d}", f"{i:07d}")       # listing order: directory by directory
         with open(p, "wb") as f:
             f.write(buf[: 4096 - (i % 3)] + bytes(i % 3))
         paths.append(p)
