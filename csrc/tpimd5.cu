@@ -404,7 +404,10 @@ static int launch_strided_tma(tpimd5_ctx *ctx, const void *base, uint64_t stride
     // integer pipes are the limit: mode 6 and the small-footprint shape.
     const bool starved = n < (uint64_t)148 * 16 * 32;
     if (shape == 0 && starved) {
-        rc = launch_tma_cfg<4, 3, 2, 4, 2>(tmap, n, (uint32_t)unit_len, table, st);
+        // at most one CTA per SM anyway (<= 74 CTAs, so that two such launches still fit side by side):
+        // four boxes per stage
+        if (n <= (uint64_t)74 * 128) rc = launch_tma_cfg<4, 1, 2, 4, 4>(tmap, n, (uint32_t)unit_len, table, st);
+        else rc = launch_tma_cfg<4, 3, 2, 4, 2>(tmap, n, (uint32_t)unit_len, table, st);
         if (rc == 0) ctx->launches.fetch_add(1);
         return rc;
     }
