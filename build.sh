@@ -3,6 +3,7 @@
 set -euo pipefail
 cd "$(dirname "$0")"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
+mkdir -p build   # ptxas log and scratch; git-ignored, so a fresh checkout has none
 OUT=terraform-provider-iterative_b200/libtpimd5.so
 $NVCC -std=c++17 -O3 -lineinfo -gencode arch=compute_100a,code=sm_100a \
       -Xcompiler -fPIC,-Wall,-Wextra,-fvisibility=hidden -Xptxas -v \

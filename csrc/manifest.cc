@@ -851,10 +851,18 @@ extern "C" void tpimd5_base64(const uint8_t md5[16], char out25[25]) {
 
 // 1 and the digest if `etag` (quotes allowed, as S3 returns it) is a plain MD5; 0 if it is a multipart
 // or otherwise opaque ETag -- then rclone falls back to the Md5chksum metadata or reports no hash.
+// [rclone v1.57.0, restated from memory, not verifiable on this box] backend/s3 lowercases the ETag and
+// strips the quotes (strings.Trim(strings.ToLower(etag), `"`)) before matching ^[0-9a-f]{32}$, so an
+// uppercase ETag from an S3-compatible store is still an MD5.
 extern "C" int tpimd5_md5_from_etag(const char *etag, uint8_t md5_out[16]) {
     if (!etag) return 0;
     std::string e(etag);
-    if (e.size() >= 2 && e.front() == '"' && e.back() == '"') e = e.substr(1, e.size() - 2);
+    for (char &c : e)
+        if (c >= 'A' && c <= 'Z') c = (char)(c - 'A' + 'a');
+    size_t lo = 0, hi = e.size();
+    while (lo < hi && e[lo] == '"') ++lo;                 // strings.Trim: every leading / trailing quote
+    while (hi > lo && e[hi - 1] == '"') --hi;
+    e = e.substr(lo, hi - lo);
     if (e.size() != 32) return 0;
     uint8_t d[16];
     for (int i = 0; i < 32; ++i) {
@@ -862,7 +870,7 @@ extern "C" int tpimd5_md5_from_etag(const char *etag, uint8_t md5_out[16]) {
         int v;
         if (c >= '0' && c <= '9') v = c - '0';
         else if (c >= 'a' && c <= 'f') v = c - 'a' + 10;
-        else return 0;                                   // uppercase is not accepted either (matchMd5 is [0-9a-f]{32})
+        else return 0;
         if (i & 1) d[i >> 1] |= (uint8_t)v; else d[i >> 1] = (uint8_t)(v << 4);
     }
     if (md5_out) memcpy(md5_out, d, 16);

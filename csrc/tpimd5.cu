@@ -58,6 +58,31 @@ static int fail(int code, const char *fmt, ...) {
                                            __FILE__, __LINE__);                                          \
     } while (0)
 
+// Makes `dev` current for the calling thread and puts the previous device back on scope exit: a caller
+// (a training process, a Go thread that cgo pinned) must not find its thread switched to another GPU.
+class DeviceGuard {
+  public:
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev_) != cudaSuccess) prev_ = -1;
+        err_ = prev_ == dev ? cudaSuccess : cudaSetDevice(dev);
+        switched_ = err_ == cudaSuccess && prev_ != dev && prev_ >= 0;
+    }
+    ~DeviceGuard() {
+        if (switched_) cudaSetDevice(prev_);
+    }
+    cudaError_t error() const { return err_; }
+    DeviceGuard(const DeviceGuard &) = delete;
+    DeviceGuard &operator=(const DeviceGuard &) = delete;
+
+  private:
+    int prev_ = -1;
+    bool switched_ = false;
+    cudaError_t err_ = cudaSuccess;
+};
+#define USE_DEVICE(dev)        \
+    DeviceGuard dev_guard_(dev); \
+    CU(dev_guard_.error())
+
 extern "C" const char *tpimd5_last_error(void) { return g_err.c_str(); }
 extern "C" void tpimd5_set_error_(const char *msg) { g_err = msg ? msg : ""; }   // for the other translation units
 extern "C" const char *tpimd5_version(void) { return "tpimd5 0.1 (sm_100a)"; }
@@ -171,6 +196,8 @@ struct Slot {
     // scratch: S3 part digests, diff tile counts
     uint8_t *d_scratch = nullptr;
     size_t scratch_cap = 0;
+    std::vector<uint8_t *> retired;   // outgrown scratch buffers: a call that captured the old pointer may still be
+                                      // launching on it, so they are only freed in tpimd5_destroy
 };
 
 struct tpimd5_ctx {
@@ -206,10 +233,12 @@ static int ensure_table(Slot &s, size_t rows) {
 
 static int ensure_scratch(Slot &s, size_t bytes) {
     if (bytes <= s.scratch_cap) return 0;
-    size_t cap = (std::max<size_t>(bytes, 1u << 20) + 255) & ~(size_t)255;
-    if (s.d_scratch) cudaFree(s.d_scratch);
-    s.d_scratch = nullptr; s.scratch_cap = 0;
-    CU(cudaMalloc(&s.d_scratch, cap));
+    // grow geometrically so that outgrown buffers (kept until destroy, see Slot::retired) stay few
+    size_t cap = (std::max<size_t>(std::max<size_t>(bytes, 2 * s.scratch_cap), 1u << 20) + 255) & ~(size_t)255;
+    uint8_t *fresh = nullptr;
+    CU(cudaMalloc(&fresh, cap));
+    if (s.d_scratch) s.retired.push_back(s.d_scratch);
+    s.d_scratch = fresh;
     s.scratch_cap = cap;
     return 0;
 }
@@ -258,7 +287,7 @@ extern "C" int tpimd5_init(const int *device_ids, int n_devices, size_t staging_
                         prop.major, prop.minor);
         std::unique_ptr<Slot> s(new Slot);
         s->dev = dev;
-        CU(cudaSetDevice(dev));
+        USE_DEVICE(dev);
         CU(cudaStreamCreateWithFlags(&s->s_copy, cudaStreamNonBlocking));
         CU(cudaStreamCreateWithFlags(&s->s_comp, cudaStreamNonBlocking));
         for (int b = 0; b < NBUF; ++b) CU(cudaStreamCreateWithFlags(&s->s_batch[b], cudaStreamNonBlocking));
@@ -275,7 +304,7 @@ extern "C" void tpimd5_destroy(tpimd5_ctx *ctx) {
     if (!ctx) return;
     for (auto &sp : ctx->slots) {
         Slot &s = *sp;
-        cudaSetDevice(s.dev);
+        DeviceGuard guard(s.dev);
         if (s.s_comp) cudaStreamSynchronize(s.s_comp);
         for (int b = 0; b < NBUF; ++b)
             if (s.s_batch[b]) { cudaStreamSynchronize(s.s_batch[b]); cudaStreamDestroy(s.s_batch[b]); }
@@ -291,6 +320,7 @@ extern "C" void tpimd5_destroy(tpimd5_ctx *ctx) {
         if (s.d_table) cudaFree(s.d_table);
         if (s.h_table) cudaFreeHost(s.h_table);
         if (s.d_scratch) cudaFree(s.d_scratch);
+        for (uint8_t *p : s.retired) cudaFree(p);
         if (s.s_copy) cudaStreamDestroy(s.s_copy);
         if (s.s_comp) cudaStreamDestroy(s.s_comp);
     }
@@ -308,25 +338,48 @@ extern "C" int tpimd5_set_variant(tpimd5_ctx *ctx, int variant) {
 // ------------------------------------------------------------------------------------------------
 // kernel launch
 // ------------------------------------------------------------------------------------------------
+// Shared-memory attributes of one kernel instantiation, for the device that is current.
 template <int CH, bool ALIGNED, int WARPS, int MINB, int MODE>
-static int launch_cfg(const LaneArgs &a, cudaStream_t st) {
+static int configure_lanes() {
     using Cfg = LaneCfg<CH, ALIGNED, WARPS>;
     auto kern = md5_lanes_kernel<CH, ALIGNED, WARPS, MINB, MODE>;
-    static thread_local int configured_dev = -1;  // per template instantiation and thread
-    int dev = 0;
-    CU(cudaGetDevice(&dev));
-    if (configured_dev != dev) {
-        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-        CU(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-        configured_dev = dev;
-    }
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    return 0;
+}
+
+// The launch alone (the instantiation must have been configured on this device).
+template <int CH, bool ALIGNED, int WARPS, int MINB, int MODE>
+static int enqueue_lanes(const LaneArgs &a, cudaStream_t st) {
+    using Cfg = LaneCfg<CH, ALIGNED, WARPS>;
     const uint64_t per_cta = WARPS * 32;
     const uint64_t grid = (a.n + per_cta - 1) / per_cta;
     if (grid == 0) return 0;
     if (grid > 0x7fffffffull) return fail(TPIMD5_ERANGE, "too many units for one launch (%llu)", (unsigned long long)a.n);
-    kern<<<(unsigned)grid, WARPS * 32, Cfg::SMEM_BYTES, st>>>(a);
+    md5_lanes_kernel<CH, ALIGNED, WARPS, MINB, MODE><<<(unsigned)grid, WARPS * 32, Cfg::SMEM_BYTES, st>>>(a);
     CU(cudaGetLastError());
     return 0;
+}
+
+// Devices on which an instantiation has been configured: one bit per device, process-wide (the
+// attribute belongs to the device's primary context, not to the calling thread).
+struct ConfiguredSet {
+    std::atomic<uint64_t> bits{0};
+    bool has(int dev) const { return dev >= 0 && dev < 64 && (bits.load(std::memory_order_acquire) >> dev) & 1; }
+    void add(int dev) { if (dev >= 0 && dev < 64) bits.fetch_or(1ull << dev, std::memory_order_release); }
+};
+
+template <int CH, bool ALIGNED, int WARPS, int MINB, int MODE>
+static int launch_cfg(const LaneArgs &a, cudaStream_t st) {
+    static ConfiguredSet configured;                 // per template instantiation
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    if (!configured.has(dev)) {
+        int rc = configure_lanes<CH, ALIGNED, WARPS, MINB, MODE>();   // idempotent: a race only repeats it
+        if (rc) return rc;
+        configured.add(dev);
+    }
+    return enqueue_lanes<CH, ALIGNED, WARPS, MINB, MODE>(a, st);
 }
 
 template <bool ALIGNED, int MODE>
@@ -370,13 +423,13 @@ template <int WARPS, int MINB, int NSTAGE, int MODE, int TILES = 1>
 static int launch_tma_cfg(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len, uint4 *table, cudaStream_t st) {
     using Cfg = StridedCfg<WARPS, NSTAGE, TILES>;
     auto kern = md5_strided_tma_kernel<WARPS, MINB, NSTAGE, MODE, TILES>;
-    static thread_local int configured_dev = -1;
+    static ConfiguredSet configured;
     int dev = 0;
     CU(cudaGetDevice(&dev));
-    if (configured_dev != dev) {
+    if (!configured.has(dev)) {
         CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
         CU(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-        configured_dev = dev;
+        configured.add(dev);
     }
     const uint64_t per_cta = WARPS * 32;
     const uint64_t grid = (n + per_cta - 1) / per_cta;
@@ -514,7 +567,7 @@ extern "C" int tpimd5_dev_hash_buffers(tpimd5_ctx *ctx, int slot, const void *d_
         if ((n - 1) > base_bytes / stride) return fail(TPIMD5_EINVAL, "dev_hash_buffers: n*stride runs past base_bytes");
         aligned = ((uintptr_t)d_base & 15) == 0 && (stride & 15) == 0;
     }
-    CU(cudaSetDevice(s->dev));
+    USE_DEVICE(s->dev);
     LaneArgs a{};
     a.base = (const uint8_t *)d_base; a.base_bytes = base_bytes;
     a.off = d_offsets; a.len = d_lengths; a.stride = stride;
@@ -573,7 +626,7 @@ extern "C" int tpimd5_dev_s3_etag(tpimd5_ctx *ctx, int slot, const void *d_data,
     if (part_size > MAX_LANE_BYTES) return fail(TPIMD5_ERANGE, "dev_s3_etag: part above %llu bytes", (unsigned long long)MAX_LANE_BYTES);
     const uint32_t np = tpimd5_s3_nparts(size, part_size);
     if (!np) return fail(TPIMD5_ERANGE, "dev_s3_etag: too many parts");
-    CU(cudaSetDevice(s->dev));
+    USE_DEVICE(s->dev);
     cudaStream_t st = (cudaStream_t)cuda_stream;
     uint8_t *parts = (uint8_t *)d_part_digests;
     if (!parts) {
@@ -612,7 +665,7 @@ extern "C" int tpimd5_dev_diff(tpimd5_ctx *ctx, int slot, const void *d_old16, c
     if (!s) return fail(TPIMD5_EINVAL, "dev_diff: bad context or slot");
     if (!d_n_changed_out) return fail(TPIMD5_EINVAL, "dev_diff: null count pointer");
     if (n > 0xffffffffull) return fail(TPIMD5_ERANGE, "dev_diff: more than 2^32 units");
-    CU(cudaSetDevice(s->dev));
+    USE_DEVICE(s->dev);
     cudaStream_t st = (cudaStream_t)cuda_stream;
     if (n == 0) {
         CU(cudaMemsetAsync(d_n_changed_out, 0, sizeof(uint64_t), st));
@@ -638,7 +691,7 @@ extern "C" int tpimd5_dev_synth_fill(tpimd5_ctx *ctx, int slot, void *d_out, uin
     if (!d_out || ((uintptr_t)d_out & 15)) return fail(TPIMD5_EINVAL, "dev_synth_fill: output must be 16-byte aligned");
     if (file_len == 0 || (file_len & 15)) return fail(TPIMD5_EINVAL, "dev_synth_fill: file_len must be a positive multiple of 16");
     if (n_files == 0) return 0;
-    CU(cudaSetDevice(s->dev));
+    USE_DEVICE(s->dev);
     const uint64_t total16 = (file_len >> 4) * n_files;
     const uint64_t want = (total16 + 255) / 256;
     const unsigned grid = (unsigned)std::min<uint64_t>(want, 148u * 64u);
@@ -653,7 +706,7 @@ extern "C" int tpimd5_dev_int_probe(tpimd5_ctx *ctx, int slot, int mode, int cta
     Slot *s = get_slot(ctx, slot);
     if (!s || !d_out || ctas_per_sm < 1 || ctas_per_sm > 16 || (mode != 0 && mode != 4 && mode != 5 && mode != 6))
         return fail(TPIMD5_EINVAL, "dev_int_probe: bad argument");
-    CU(cudaSetDevice(s->dev));
+    USE_DEVICE(s->dev);
     int sms = 0;
     CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->dev));
     const unsigned grid = (unsigned)(sms * ctas_per_sm);
@@ -764,7 +817,7 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
         std::stable_sort(by_size.begin(), by_size.end(), [&](uint32_t a, uint32_t b) { return job.len[a] > job.len[b]; });
     }
     const std::vector<uint32_t> &units = job.paths ? by_size : units_in;
-    CU(cudaSetDevice(s.dev));
+    USE_DEVICE(s.dev);
     s.stage_bytes = ctx->staging;
     int rc = ensure_table(s, units.size());
     if (rc) return rc;
@@ -1005,7 +1058,7 @@ static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint
     const int rc = run_device_impl(ctx, s, job, units);
     if (rc != 0) {
         const std::string keep = g_err;                 // the first error is the one to report
-        cudaSetDevice(s.dev);
+        DeviceGuard guard(s.dev);
         cudaStreamSynchronize(s.s_copy);
         for (int b = 0; b < NBUF; ++b)
             if (s.s_batch[b]) cudaStreamSynchronize(s.s_batch[b]);
@@ -1164,11 +1217,8 @@ extern "C" int tpimd5_diff(tpimd5_ctx *ctx, const uint8_t *old16, const uint8_t 
     if (n > 0xffffffffull) return fail(TPIMD5_ERANGE, "diff: more than 2^32 units");
     Slot &s = *ctx->slots[0];
     std::lock_guard<std::mutex> guard(s.mu);
-    CU(cudaSetDevice(s.dev));
-    {
-        int rc0 = ensure_scratch(s, ((n + DIFF_TILE - 1) / DIFF_TILE) * sizeof(uint64_t));
-        if (rc0) return rc0;
-    }
+    USE_DEVICE(s.dev);
+    const size_t tiles = (n + DIFF_TILE - 1) / DIFF_TILE;   // tile counts: this call's own, not the slot's dev_* scratch
     uint8_t *d_old = nullptr, *d_new = nullptr;
     uint32_t *d_idx = nullptr;
     uint64_t *d_cnt = nullptr;
@@ -1191,10 +1241,10 @@ extern "C" int tpimd5_diff(tpimd5_ctx *ctx, const uint8_t *old16, const uint8_t 
     CUX(cudaMalloc(&d_old, n * 16));
     CUX(cudaMalloc(&d_new, n * 16));
     CUX(cudaMalloc(&d_idx, n * 4));
-    CUX(cudaMalloc(&d_cnt, 8));
+    CUX(cudaMalloc(&d_cnt, 8 + tiles * sizeof(uint64_t)));
     CUX(cudaMemcpyAsync(d_old, old16, n * 16, cudaMemcpyHostToDevice, s.s_comp));
     CUX(cudaMemcpyAsync(d_new, new16, n * 16, cudaMemcpyHostToDevice, s.s_comp));
-    rc = diff_launch(ctx, d_old, d_new, n, d_idx, d_cnt, (uint64_t *)s.d_scratch, s.s_comp);
+    rc = diff_launch(ctx, d_old, d_new, n, d_idx, d_cnt, d_cnt + 1, s.s_comp);
     if (rc) { cleanup(); return rc; }
     CUX(cudaMemcpyAsync(&cnt, d_cnt, 8, cudaMemcpyDeviceToHost, s.s_comp));
     CUX(cudaStreamSynchronize(s.s_comp));
@@ -1365,9 +1415,10 @@ extern "C" int tpimd5_dev_s3_etag_noalloc(int device, const void *d_data, uint64
                     "s3_etag_noalloc: %llu parts, but the built-in scratch holds %d part digests; use a larger part_size "
                     "(tpimd5_s3_part_size) or tpimd5_dev_s3_etag",
                     (unsigned long long)np, TPIMD5_NOALLOC_MAX_PARTS);
-    CU(cudaSetDevice(device));
+    USE_DEVICE(device);
 
-    // set-up, first call on this device: where does the array live on *this* GPU?
+    // set-up, first call on this device (any thread): where does the array live on *this* GPU, and the
+    // shared-memory attributes of the two kernel instantiations this entry point can launch
     uint8_t *parts;
     {
         std::lock_guard<std::mutex> g(g_noalloc_mu);
@@ -1375,22 +1426,28 @@ extern "C" int tpimd5_dev_s3_etag_noalloc(int device, const void *d_data, uint64
             uint8_t *ptr = nullptr;
             CU(cudaGetSymbolAddress((void **)&ptr, g_noalloc_part_digests));
             if (!ptr) return fail(TPIMD5_ECUDA, "s3_etag_noalloc: no device address for the scratch array on device %d", device);
+            int rc = configure_lanes<256, true, 4, 3, 4>();
+            if (rc == 0) rc = configure_lanes<256, false, 4, 3, 4>();
+            if (rc) return rc;
             g_noalloc_dev_ptr[device] = ptr;
         }
         parts = g_noalloc_dev_ptr[device];
     }
 
     cudaStream_t st = (cudaStream_t)cuda_stream;
+    // At most 10,000 chains: far too few to fill the SMs, so every chain runs at its dependent-op latency.
+    // Same choice as launch_lanes makes for such launches: 256-byte stages and the step formulation with
+    // the shortest dependent chain (mode 4).
     // per-part MD5s into the built-in array (one lane per part) ...
     LaneArgs a{};
     a.base = (const uint8_t *)d_data; a.base_bytes = size; a.stride = part_size;
     a.table = (uint4 *)parts; a.n = np;
     const bool aligned = ((uintptr_t)d_data & 15) == 0 && (part_size & 15) == 0;
-    int rc = aligned ? launch_cfg<128, true, 4, 5, 0>(a, st) : launch_cfg<128, false, 4, 5, 0>(a, st);
+    int rc = aligned ? enqueue_lanes<256, true, 4, 3, 4>(a, st) : enqueue_lanes<256, false, 4, 3, 4>(a, st);
     if (rc) return rc;
     // ... then the MD5 of those 16*np bytes, read back from the same array
     LaneArgs b{};
     b.base = parts; b.base_bytes = np * 16; b.stride = np * 16;
     b.table = (uint4 *)d_etag_md5_out; b.n = 1;
-    return launch_cfg<128, true, 4, 5, 0>(b, st);
+    return enqueue_lanes<256, true, 4, 3, 4>(b, st);
 }

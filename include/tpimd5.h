@@ -88,8 +88,10 @@ TPIMD5_API int tpimd5_s3_etag_file(tpimd5_ctx *ctx, const char *path, uint64_t s
  * The textual forms the back-ends exchange ([rclone] backend/s3, azureblob, googlecloudstorage;
  * registered at storage.go:18-21): lowercase hex (rclone hash strings, plain S3 ETags), base64
  * (Content-MD5 per part / per object, X-Amz-Meta-Md5chksum, Azure Content-MD5, GCS md5Hash), the
- * multipart ETag "<hex>-<nparts>", and rclone's test whether an ETag is an MD5 at all
- * (exactly 32 lowercase hex digits; returns 1 and the bytes, else 0). */
+ * multipart ETag "<hex>-<nparts>", and rclone's test whether an ETag is an MD5 at all (after
+ * lowercasing and stripping quotes: exactly 32 hex digits; returns 1 and the bytes, else 0).
+ * Every "[rclone]" rule in this header is restated from knowledge of v1.57.0; the module's source
+ * is not on this machine, so fidelity to it cannot be verified here. */
 TPIMD5_API void tpimd5_hex(const uint8_t md5[16], char out33[33]);
 TPIMD5_API void tpimd5_base64(const uint8_t md5[16], char out25[25]);
 TPIMD5_API int tpimd5_md5_from_etag(const char *etag, uint8_t md5_out[16]);
@@ -195,9 +197,13 @@ TPIMD5_API int tpimd5_transfer_local(tpimd5_ctx *ctx, const char *source, const 
  *   the host-pointer calls have no such limit, they chain a long unit across launches.
  *   Scratch: hash_buffers with offset arrays (>= 4,096 units are bucketed by length with a
  *   device radix sort), s3_etag with d_part_digests == NULL, and diff (tile counts) keep their
- *   temporaries in one per-slot buffer that grows on demand (cudaMalloc on first use).  Calls
+ *   temporaries in one per-slot buffer that grows on demand (cudaMalloc on first use; an outgrown
+ *   buffer stays allocated until tpimd5_destroy, so a call never launches on freed memory).  Calls
  *   that use it on the same slot must not overlap on the GPU: keep them on one stream, or pass
- *   your own part-digest buffer, or use one slot (device) per stream. */
+ *   your own part-digest buffer, or use one slot (device) per stream.  The host-pointer calls
+ *   (tpimd5_diff, tpimd5_plan_transfer, tpimd5_transfer_local, ...) never touch this buffer.
+ *   Every tpimd5_dev_* call makes the slot's device current while it runs and restores the calling
+ *   thread's previous device before it returns. */
 TPIMD5_API int tpimd5_dev_hash_buffers(tpimd5_ctx *ctx, int slot, const void *d_base, uint64_t base_bytes,
                             const uint64_t *d_offsets, const uint64_t *d_lengths, uint64_t stride, size_t n,
                             void *d_digests_out, void *cuda_stream);
@@ -238,8 +244,12 @@ TPIMD5_API int tpimd5_dev_synth_fill(tpimd5_ctx *ctx, int slot, void *d_out, uin
  *     and both ETags are garbage.  Keep such calls on one stream or order them with events.
  *   - the array keeps the previous call's contents.  Nothing here needs it to start at zero: the
  *     second kernel reads exactly the 16 * nparts bytes the first kernel of the same call wrote.
- *   - the first call on each device looks up the array's device address and sets the kernels'
- *     shared-memory attributes; make that first call before any stream capture begins. */
+ *   - the first call on each device (whichever thread makes it) looks up the array's device address
+ *     and sets the shared-memory attributes of both kernel forms the call can launch (16-byte
+ *     aligned input, and any other alignment); later calls on that device, from any thread, only
+ *     enqueue.  Make that first call before any stream capture begins.
+ *   - `device` is made current for the duration of the call and the thread's previous device is
+ *     restored before returning, also on errors (as in every tpimd5_dev_* call). */
 #define TPIMD5_NOALLOC_MAX_PARTS 10000
 TPIMD5_API int tpimd5_dev_s3_etag_noalloc(int device, const void *d_data, uint64_t size, uint64_t part_size,
                                           void *d_etag_md5_out, void *cuda_stream);

@@ -152,7 +152,7 @@ def md5_base64(md5: bytes) -> str:
 
 
 def md5_from_etag(etag: str) -> Optional[bytes]:
-    """rclone's rule: an S3 ETag is an MD5 only if it is exactly 32 lowercase hex digits."""
+    """rclone's rule: an S3 ETag is an MD5 only if, lowercased and without quotes, it is exactly 32 hex digits."""
     d = (C.c_uint8 * 16)()
     return bytes(d) if load_library().tpimd5_md5_from_etag(etag.encode(), d) == 1 else None
 
