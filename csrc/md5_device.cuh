@@ -61,10 +61,27 @@ __host__ __device__ constexpr int fma_step(int i) {
     return MODE == 5 ? 1 : MODE == 6 ? (i & 1) : 0;
 }
 
+// m + k as an IMAD by the constant-bank 1 with k as the immediate addend: the fma pipe, whatever ptxas
+// would choose for a plain add
+__device__ __forceinline__ uint32_t madk(uint32_t m, uint32_t k) {
+    uint32_t r;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(m), "r"(c_one), "r"(k));
+    return r;
+}
+
 template <int MODE, int FMA_FORM>
 __device__ __forceinline__ uint32_t step_sum(uint32_t a, uint32_t f, uint32_t m, uint32_t k) {
     if (MODE == 0) {
         return (a + (m + k)) + f;
+    } else if (MODE == 7) {
+        // experimental: a + m + k as one three-input add off the chain (alu), then a two-input add on it
+        uint32_t x;
+        asm("{\n\t.reg .u32 t;\n\tadd.u32 t, %1, %2;\n\tadd.u32 %0, t, %3;\n\t}" : "=r"(x) : "r"(a), "r"(m), "r"(k));
+        return x + f;
+    } else if (MODE == 8) {
+        // experimental: m + k on the fma pipe for certain (IMAD), the rest as mode 4
+        const uint32_t x = madk(m, k);
+        return a + x + f;
     } else if (!FMA_FORM) {
         const uint32_t x = add_imm(m, k);
         return a + x + f;

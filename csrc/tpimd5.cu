@@ -33,6 +33,7 @@
 #include "aux_kernels.cuh"
 #include "md5_lanes.cuh"
 #include "md5_strided_tma.cuh"
+#include "md5_chain_tma.cuh"
 
 using namespace tpimd5;
 
@@ -330,7 +331,7 @@ extern "C" void tpimd5_destroy(tpimd5_ctx *ctx) {
 extern "C" int tpimd5_ctx_devices(const tpimd5_ctx *ctx) { return ctx ? (int)ctx->slots.size() : 0; }
 extern "C" uint64_t tpimd5_launch_count(const tpimd5_ctx *ctx) { return ctx ? ctx->launches.load() : 0; }
 extern "C" int tpimd5_set_variant(tpimd5_ctx *ctx, int variant) {
-    if (!ctx || variant < 0 || variant > 299) return fail(TPIMD5_EINVAL, "tpimd5_set_variant: 100*loader(0 cp.async, 1 bulk, 2 tensor map for strided units) + 10*mode(0,4,6) + shape");
+    if (!ctx || variant < 0 || variant > 399) return fail(TPIMD5_EINVAL, "tpimd5_set_variant: 100*loader(0 cp.async, 2 tensor map for strided units, 3 latency kernel for strided units) + 10*mode(0,4,6) + shape");
     ctx->variant = variant;
     return 0;
 }
@@ -438,9 +439,48 @@ static int launch_tma_cfg(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len
     return 0;
 }
 
+template <int WARPS, int MINB, int NSTAGE, int TILES, int MODE>
+static int launch_chain_cfg(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len, uint4 *table, cudaStream_t st) {
+    using Cfg = ChainCfg<WARPS, NSTAGE, TILES>;
+    auto kern = md5_chain_tma_kernel<WARPS, MINB, NSTAGE, TILES, MODE>;
+    static ConfiguredSet configured;
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    if (!configured.has(dev)) {
+        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+        CU(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        configured.add(dev);
+    }
+    const uint64_t per_cta = WARPS * 32;
+    const uint64_t grid = (n + per_cta - 1) / per_cta;
+    kern<<<(unsigned)grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(tmap, n, unit_len, table);
+    CU(cudaGetLastError());
+    return 0;
+}
+
+// The latency kernel (md5_chain_tma.cuh) in one of its shapes; mode 4 unless 0 or 6 is asked for.
+static int launch_chain(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len, uint4 *table, int shape, int mode, cudaStream_t st) {
+#define TPI_CHAIN(M)                                                                           \
+    switch (shape) {                                                                           \
+        default:                                                                               \
+        case 1: return launch_chain_cfg<4, 1, 2, 4, M>(tmap, n, unit_len, table, st);          \
+        case 2: return launch_chain_cfg<4, 1, 4, 2, M>(tmap, n, unit_len, table, st);          \
+        case 3: return launch_chain_cfg<4, 3, 2, 2, M>(tmap, n, unit_len, table, st);          \
+        case 4: return launch_chain_cfg<4, 3, 4, 1, M>(tmap, n, unit_len, table, st);          \
+        case 5: return launch_chain_cfg<4, 6, 2, 1, M>(tmap, n, unit_len, table, st);          \
+        case 6: return launch_chain_cfg<2, 2, 4, 2, M>(tmap, n, unit_len, table, st);          \
+        case 7: return launch_chain_cfg<4, 1, 8, 1, M>(tmap, n, unit_len, table, st);          \
+        case 8: return launch_chain_cfg<2, 4, 2, 2, M>(tmap, n, unit_len, table, st);          \
+    }
+    if (mode == 0) { TPI_CHAIN(0) }
+    if (mode == 6) { TPI_CHAIN(6) }
+    TPI_CHAIN(4)
+#undef TPI_CHAIN
+}
+
 // n units of unit_len bytes, unit u at base + u*stride.  shape: 1..4, mode 0 or 4.
 static int launch_strided_tma(tpimd5_ctx *ctx, const void *base, uint64_t stride, uint64_t unit_len, uint64_t n, uint4 *table,
-                              int shape, int mode, cudaStream_t st) {
+                              int loader, int shape, int mode, cudaStream_t st) {
     CUtensorMap tmap;
     const cuuint64_t gdim[2] = {unit_len, n};
     const cuuint64_t gstride[1] = {stride};
@@ -451,16 +491,28 @@ static int launch_strided_tma(tpimd5_ctx *ctx, const void *base, uint64_t stride
                                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(TPIMD5_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
     int rc;
-    // Too few chains to fill the SMs (fewer than 16 warps per SM): every chain runs at its dependent-op
-    // latency, so pick the formulation with the shortest chain (mode 4: LOP3 -> IADD3 -> LEA.HI, all on
-    // one pipe) and the kernel shape with the least per-stage work on that chain.  Otherwise the
-    // integer pipes are the limit: mode 6 and the small-footprint shape.
-    const bool starved = n < (uint64_t)148 * 16 * 32;
-    if (shape == 0 && starved) {
-        // at most one CTA per SM anyway (<= 74 CTAs, so that two such launches still fit side by side):
-        // four boxes per stage
-        if (n <= (uint64_t)74 * 128) rc = launch_tma_cfg<4, 1, 2, 4, 4>(tmap, n, (uint32_t)unit_len, table, st);
-        else rc = launch_tma_cfg<4, 3, 2, 4, 2>(tmap, n, (uint32_t)unit_len, table, st);
+    if (loader == 3) {
+        rc = launch_chain(tmap, n, (uint32_t)unit_len, table, shape, mode, st);
+        if (rc == 0) ctx->launches.fetch_add(1);
+        return rc;
+    }
+    // Too few chains to fill the SMs: every chain runs at its dependent-op latency, so the launch goes to
+    // the latency kernel (md5_chain_tma.cuh; mode 4 = LOP3 -> IADD3 -> LEA.HI, the shortest chain), in the
+    // shape that spreads its warps thinnest over the SM sub-partitions (measured, profiles/r2_chain_sweep.md):
+    //   <= 148 warps             2 hashing warps per CTA, <= 74 CTAs: one warp per sub-partition, and two
+    //                            such launches still fit side by side (two S3 files on two streams)
+    //   <= 592 warps             4 hashing warps per CTA, one CTA per SM (128 KiB of stages each)
+    //   <= 888 warps             2 per CTA, up to three CTAs per SM: at most two warps per sub-partition
+    //   <= 1,776 warps           4 per CTA, up to three CTAs per SM; three warps share a sub-partition, where
+    //                            the integer pipes start to bind: the step formulation that splits the adds (6)
+    // Beyond that (12 warps per SM would no longer hold the launch in one wave) the throughput kernel below.
+    const uint64_t warps = (n + 31) / 32;
+    if (shape == 0 && warps <= (uint64_t)148 * 12) {
+        const uint32_t ul = (uint32_t)unit_len;
+        if (warps <= 148) rc = launch_chain_cfg<2, 2, 4, 2, 4>(tmap, n, ul, table, st);
+        else if (warps <= 592) rc = launch_chain_cfg<4, 1, 2, 4, 4>(tmap, n, ul, table, st);
+        else if (warps <= 888) rc = launch_chain_cfg<2, 2, 4, 2, 4>(tmap, n, ul, table, st);
+        else rc = launch_chain_cfg<4, 3, 2, 2, 6>(tmap, n, ul, table, st);
         if (rc == 0) ctx->launches.fetch_add(1);
         return rc;
     }
@@ -533,8 +585,8 @@ static int launch_strided(tpimd5_ctx *ctx, const void *base, uint64_t base_bytes
     int loader, mode, shape;
     decode_variant(ctx->variant.load(), loader, mode, shape);
     const uint64_t n_full = std::min<uint64_t>(n, base_bytes / stride);
-    if (loader == 2 && n_full && tma_eligible(base, stride, stride, n_full)) {
-        int rc = launch_strided_tma(ctx, base, stride, stride, n_full, table, shape, mode, st);
+    if (loader >= 2 && n_full && tma_eligible(base, stride, stride, n_full)) {
+        int rc = launch_strided_tma(ctx, base, stride, stride, n_full, table, loader, shape, mode, st);
         if (rc || n_full == n) return rc;
         a.base += n_full * stride; a.base_bytes -= n_full * stride; a.table += n_full; a.n = n - n_full;
     }
@@ -641,10 +693,8 @@ extern "C" int tpimd5_dev_s3_etag(tpimd5_ctx *ctx, int slot, const void *d_data,
     int rc = launch_strided(ctx, d_data, size, part_size, np, (uint4 *)parts, st);
     if (rc) return rc;
     // K2b: digest of digests -- the part digests are one more message of 16*np bytes
-    LaneArgs b{};
-    b.base = parts; b.base_bytes = (uint64_t)np * 16; b.stride = (uint64_t)np * 16;
-    b.table = (uint4 *)d_etag_md5_out; b.n = 1;
-    return launch_lanes(ctx, b, true, st);
+    // (one chain: the latency kernel, fed by TMA like the parts)
+    return launch_strided(ctx, parts, (uint64_t)np * 16, (uint64_t)np * 16, 1, (uint4 *)d_etag_md5_out, st);
 }
 
 // three launches: per-tile counts, exclusive scan of the counts, ordered scatter
@@ -704,7 +754,7 @@ extern "C" int tpimd5_dev_synth_fill(tpimd5_ctx *ctx, int slot, void *d_out, uin
 extern "C" int tpimd5_dev_int_probe(tpimd5_ctx *ctx, int slot, int mode, int ctas_per_sm, uint32_t iters, void *d_out,
                                     uint64_t *blocks_out, void *cuda_stream) {
     Slot *s = get_slot(ctx, slot);
-    if (!s || !d_out || ctas_per_sm < 1 || ctas_per_sm > 16 || (mode != 0 && mode != 4 && mode != 5 && mode != 6))
+    if (!s || !d_out || ctas_per_sm < 1 || ctas_per_sm > 16 || (mode != 0 && (mode < 4 || mode > 8)))
         return fail(TPIMD5_EINVAL, "dev_int_probe: bad argument");
     USE_DEVICE(s->dev);
     int sms = 0;
@@ -715,6 +765,8 @@ extern "C" int tpimd5_dev_int_probe(tpimd5_ctx *ctx, int slot, int mode, int cta
         case 0: int_probe_kernel<0><<<grid, 128, 0, st>>>(iters, (uint4 *)d_out); break;
         case 4: int_probe_kernel<4><<<grid, 128, 0, st>>>(iters, (uint4 *)d_out); break;
         case 5: int_probe_kernel<5><<<grid, 128, 0, st>>>(iters, (uint4 *)d_out); break;
+        case 7: int_probe_kernel<7><<<grid, 128, 0, st>>>(iters, (uint4 *)d_out); break;
+        case 8: int_probe_kernel<8><<<grid, 128, 0, st>>>(iters, (uint4 *)d_out); break;
         default: int_probe_kernel<6><<<grid, 128, 0, st>>>(iters, (uint4 *)d_out); break;
     }
     CU(cudaGetLastError());
@@ -1206,6 +1258,87 @@ extern "C" int tpimd5_s3_etag_file(tpimd5_ctx *ctx, const char *path, uint64_t s
                                    uint8_t *part_digests_out, uint8_t etag_md5_out[16], uint32_t *nparts_out) {
     if (!path) return fail(TPIMD5_EINVAL, "s3_etag_file: null path");
     return s3_common(ctx, nullptr, path, size, part_size, part_digests_out, etag_md5_out, nparts_out);
+}
+
+// ------------------------------------------------------------------------------------------------
+// S3 upload plan: what [rclone v1.57.0] backend/s3 Object.Update needs to know about one local file
+// before it sends a byte (rule restated from memory of that release)
+// ------------------------------------------------------------------------------------------------
+extern "C" uint32_t tpimd5_s3_plan_parts(uint64_t size, uint64_t chunk_size, uint64_t upload_cutoff, uint32_t max_parts,
+                                         int *multipart_out, uint64_t *part_size_out) {
+    if (!chunk_size) chunk_size = (uint64_t)5 << 20;          // rclone: chunk_size default (and minimum) 5 MiB
+    if (!upload_cutoff) upload_cutoff = (uint64_t)200 << 20;  // upload_cutoff default 200 MiB
+    if (!max_parts) max_parts = 10000;                        // max_upload_parts default
+    const bool multi = size >= upload_cutoff;                 // "multipart := size < 0 || size >= upload_cutoff"
+    uint64_t part = size;
+    uint32_t np = 1;
+    if (multi) {
+        part = tpimd5_s3_part_size(size, chunk_size, max_parts);
+        np = tpimd5_s3_nparts(size, part);
+    }
+    if (multipart_out) *multipart_out = multi ? 1 : 0;
+    if (part_size_out) *part_size_out = part;
+    return np;
+}
+
+extern "C" int tpimd5_s3_upload_plan(tpimd5_ctx *ctx, const char *path, uint64_t size, uint64_t chunk_size, uint64_t upload_cutoff,
+                                     uint32_t max_parts, uint32_t flags, tpimd5_s3_plan *plan_out, uint8_t *part_md5_out,
+                                     char *part_content_md5_out) {
+    if (!ctx || !path || !plan_out) return fail(TPIMD5_EINVAL, "s3_upload_plan: null pointer");
+    memset(plan_out, 0, sizeof *plan_out);
+    int multi = 0;
+    uint64_t part = 0;
+    const uint32_t np = tpimd5_s3_plan_parts(size, chunk_size, upload_cutoff, max_parts, &multi, &part);
+    if (!np) return fail(TPIMD5_ERANGE, "s3_upload_plan: too many parts");
+    const bool whole = !multi || !(flags & TPIMD5_PLAN_NO_WHOLE_MD5);
+    struct stat sb;
+    if (stat(path, &sb) != 0) return fail(TPIMD5_EIO, "%s: %s", path, strerror(errno));
+    if ((uint64_t)sb.st_size != size)
+        return fail(TPIMD5_EIO, "%s: size is %llu, not the listed %llu bytes", path, (unsigned long long)sb.st_size,
+                    (unsigned long long)size);
+    // one job: the parts (multipart only) and, unless switched off, the whole file as one more unit --
+    // both read the same bytes, so the second read comes out of the page cache
+    const size_t nu = (multi ? np : 0) + (whole ? 1 : 0);
+    std::vector<uint64_t> off(nu), len(nu);
+    std::vector<const char *> same(nu, path);
+    std::vector<uint8_t> dig(nu * 16);
+    size_t k = 0;
+    if (whole) { off[k] = 0; len[k] = size; ++k; }             // first: it is the longest chain by far
+    if (multi)
+        for (uint32_t i = 0; i < np; ++i, ++k) {
+            off[k] = (uint64_t)i * part;
+            len[k] = std::min(part, size - off[k]);
+        }
+    Job job;
+    job.n = nu; job.len = len.data(); job.out = dig.data(); job.paths = same.data(); job.file_off = off.data();
+    int rc = run_job(ctx, job);
+    if (rc) return rc;
+    plan_out->multipart = multi;
+    plan_out->part_size = part;
+    plan_out->nparts = np;
+    plan_out->has_md5 = whole ? 1 : 0;
+    const uint8_t *parts = dig.data() + (whole ? 16 : 0);
+    if (whole) {
+        memcpy(plan_out->md5, dig.data(), 16);
+        tpimd5_base64(plan_out->md5, plan_out->content_md5);   // Content-MD5 (single) / X-Amz-Meta-Md5chksum (multipart)
+    }
+    if (!multi) {
+        tpimd5_hex(plan_out->md5, plan_out->etag);              // a plain PutObject answers with the MD5 as its ETag
+        if (part_md5_out) memcpy(part_md5_out, plan_out->md5, 16);
+        if (part_content_md5_out) memcpy(part_content_md5_out, plan_out->content_md5, 25);
+        return 0;
+    }
+    if (part_md5_out) memcpy(part_md5_out, parts, (size_t)np * 16);
+    if (part_content_md5_out)
+        for (uint32_t i = 0; i < np; ++i) tpimd5_base64(parts + 16 * (size_t)i, part_content_md5_out + 25 * (size_t)i);
+    // expected ETag: MD5 of the concatenated part digests, hashed on the GPU like everything else
+    uint8_t etag_md5[16];
+    const uint64_t zero = 0, dl = (uint64_t)np * 16;
+    Job j2;
+    j2.n = 1; j2.base = parts; j2.off = &zero; j2.len = &dl; j2.out = etag_md5;
+    rc = run_job(ctx, j2);
+    if (rc) return rc;
+    return tpimd5_s3_etag_text(etag_md5, np, plan_out->etag, sizeof plan_out->etag);
 }
 
 extern "C" int tpimd5_diff(tpimd5_ctx *ctx, const uint8_t *old16, const uint8_t *new16, size_t n, uint32_t *changed_idx_out,

@@ -84,6 +84,35 @@ TPIMD5_API int tpimd5_s3_etag_buffer(tpimd5_ctx *ctx, const uint8_t *data, uint6
 TPIMD5_API int tpimd5_s3_etag_file(tpimd5_ctx *ctx, const char *path, uint64_t size, uint64_t part_size,
                         uint8_t *part_digests_out, uint8_t etag_md5_out[16], uint32_t *nparts_out);
 
+/* ---- S3 upload plan -------------------------------------------------------------------------
+ * Everything [rclone] backend/s3 Object.Update decides and computes about one local file before it
+ * uploads it (call path storage.go:21 -> sync.CopyDir storage.go:158 -> operations.Copy): below
+ * upload_cutoff a single PutObject with Content-MD5 = base64 of the whole-file MD5 (the ETag S3 then
+ * answers with is that MD5 in hex); at or above it a multipart upload with the part size of
+ * tpimd5_s3_part_size, one base64 Content-MD5 per UploadPart, the whole-file MD5 kept as metadata
+ * X-Amz-Meta-Md5chksum (base64), and the ETag expected back: hex(md5(part digests)) + "-" + nparts.
+ * Zero for chunk_size / upload_cutoff / max_parts selects rclone's defaults (5 MiB, 200 MiB, 10,000).
+ * TPIMD5_PLAN_NO_WHOLE_MD5 is rclone's --s3-disable-checksum: skip the whole-file MD5 of a multipart
+ * object (one serial chain: by far the slowest unit of a large file on a GPU).
+ * tpimd5_s3_plan_parts is the pure decision (no I/O): the part count to size the output arrays with.
+ * part_md5_out: 16*nparts bytes or NULL; part_content_md5_out: 25*nparts chars (NUL-terminated base64
+ * strings) or NULL.  The rule is restated from knowledge of rclone v1.57.0, not verifiable here. */
+#define TPIMD5_PLAN_NO_WHOLE_MD5 1u
+typedef struct tpimd5_s3_plan {
+    int32_t multipart;        /* 0 = single PutObject, 1 = multipart upload                      */
+    int32_t has_md5;          /* whole-file MD5 computed (always for a single PutObject)         */
+    uint64_t part_size;       /* multipart: bytes per part (the last may be shorter); else size  */
+    uint32_t nparts;          /* multipart: parts; else 1                                        */
+    uint8_t md5[16];          /* whole-file MD5                                                  */
+    char content_md5[25];     /* its base64: Content-MD5 (single) / Md5chksum metadata (multi)   */
+    char etag[48];            /* ETag to expect back: 32 hex, or 32 hex + "-" + nparts           */
+} tpimd5_s3_plan;
+TPIMD5_API uint32_t tpimd5_s3_plan_parts(uint64_t size, uint64_t chunk_size, uint64_t upload_cutoff, uint32_t max_parts,
+                                         int *multipart_out, uint64_t *part_size_out);
+TPIMD5_API int tpimd5_s3_upload_plan(tpimd5_ctx *ctx, const char *path, uint64_t size, uint64_t chunk_size,
+                                     uint64_t upload_cutoff, uint32_t max_parts, uint32_t flags, tpimd5_s3_plan *plan_out,
+                                     uint8_t *part_md5_out, char *part_content_md5_out);
+
 /* ---- digest strings -----------------------------------------------------------------------
  * The textual forms the back-ends exchange ([rclone] backend/s3, azureblob, googlecloudstorage;
  * registered at storage.go:18-21): lowercase hex (rclone hash strings, plain S3 ETags), base64

@@ -65,6 +65,8 @@ def lib() -> C.CDLL:
         L.orc_equal.restype = C.c_int
         L.orc_synth_fill.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint64]
         L.orc_synth_fill.restype = None
+        L.orc_synth_fill_files.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_int]
+        L.orc_synth_fill_files.restype = None
         L.orc_has_openssl.restype = C.c_int
         L.orc_md5_files.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int]
         L.orc_md5_files.restype = C.c_int
@@ -174,6 +176,35 @@ def s3_etag_text(etag_md5: bytes, nparts: int) -> str:
     return f"{etag_md5.hex()}-{nparts}"
 
 
+def md5_from_etag(etag: str) -> Optional[bytes]:
+    """rclone backend/s3: the ETag, lowercased and with its quotes trimmed, is the object's MD5 iff it matches
+    ^[0-9a-f]{32}$ (so never for multipart "-N" or SSE-KMS ETags).  Restated from memory of v1.57.0."""
+    e = etag.lower().strip('"')
+    return bytes.fromhex(e) if re.fullmatch(r"[0-9a-f]{32}", e) else None
+
+
+def s3_upload_plan(data, chunk_size: int = 5 << 20, upload_cutoff: int = 200 << 20, max_parts: int = 10000,
+                   whole_md5: bool = True) -> dict:
+    """What rclone v1.57.0 backend/s3 Object.Update computes for one object before uploading it (SURVEY.md
+    appendix C; restated from memory, the module is not on this machine): a single PutObject below
+    upload_cutoff (Content-MD5 = base64 MD5, ETag = hex MD5), else multipart: part size by the growth rule,
+    a base64 Content-MD5 per part, Md5chksum metadata = base64 whole-file MD5, ETag hex(md5(md5s))-N."""
+    import base64
+    a = _as_u8(data)
+    multi = a.size >= upload_cutoff
+    whole = md5(a) if (whole_md5 or not multi) else None
+    if not multi:
+        return {"multipart": False, "part_size": a.size, "nparts": 1, "md5": whole,
+                "content_md5": base64.b64encode(whole).decode(), "etag": whole.hex(),
+                "part_md5": np.frombuffer(whole, dtype=np.uint8).reshape(1, 16).copy(),
+                "part_content_md5": [base64.b64encode(whole).decode()]}
+    part = s3_part_size(a.size, chunk_size, max_parts)
+    etag, n, parts = s3_etag(a, part)
+    return {"multipart": True, "part_size": part, "nparts": n, "md5": whole,
+            "content_md5": base64.b64encode(whole).decode() if whole else None, "etag": s3_etag_text(etag, n),
+            "part_md5": parts, "part_content_md5": [base64.b64encode(bytes(p)).decode() for p in parts]}
+
+
 def diff(old16, new16) -> np.ndarray:
     o, n = _as_u8(old16).reshape(-1, 16), _as_u8(new16).reshape(-1, 16)
     assert o.shape == n.shape
@@ -201,6 +232,17 @@ def synth_bytes(seed: int, file_index: int, n: int, byte_offset: int = 0) -> np.
     out = np.empty(n, dtype=np.uint8)
     if n:
         lib().orc_synth_fill(seed, file_index, byte_offset, out.ctypes.data, n)
+    return out
+
+
+def synth_files(seed: int, first_index: int, file_len: int, n_files: int, out: Optional[np.ndarray] = None,
+                threads: int = 1) -> np.ndarray:
+    """n_files equal files back to back (file i at i*file_len): the packed synthetic workdir, filled by `threads` workers."""
+    if out is None:
+        out = np.empty(file_len * n_files, dtype=np.uint8)
+    assert out.dtype == np.uint8 and out.size >= file_len * n_files and out.flags["C_CONTIGUOUS"]
+    if file_len * n_files:
+        lib().orc_synth_fill_files(seed, first_index, file_len, n_files, out.ctypes.data, threads)
     return out
 
 

@@ -335,6 +335,47 @@ void orc_synth_fill(uint64_t seed, uint64_t file_index, uint64_t byte_offset, ui
     }
 }
 
+/* n_files files of file_len bytes each, file f = first_index + i at out + i*file_len: the packed
+ * synthetic workdir (bench.py / tests fill multi-GiB host buffers with it), nthreads workers. */
+typedef struct {
+    uint64_t seed, first, file_len, n;
+    uint8_t *out;
+    size_t *next;
+    pthread_mutex_t *mu;
+} fill_job;
+
+static void *fill_worker(void *arg) {
+    fill_job *j = (fill_job *)arg;
+    for (;;) {
+        pthread_mutex_lock(j->mu);
+        size_t lo = *j->next;
+        size_t step = j->file_len >= (1u << 20) ? 1 : (size_t)((1u << 20) / (j->file_len ? j->file_len : 1));
+        size_t hi = lo + step < j->n ? lo + step : j->n;
+        *j->next = hi;
+        pthread_mutex_unlock(j->mu);
+        if (lo >= j->n) break;
+        for (size_t i = lo; i < hi; i++) orc_synth_fill(j->seed, j->first + i, 0, j->out + i * j->file_len, j->file_len);
+    }
+    return NULL;
+}
+
+void orc_synth_fill_files(uint64_t seed, uint64_t first_index, uint64_t file_len, uint64_t n_files, uint8_t *out,
+                          int nthreads) {
+    if (nthreads < 1) nthreads = 1;
+    if (nthreads > 256) nthreads = 256;
+    size_t next = 0;
+    pthread_mutex_t mu = PTHREAD_MUTEX_INITIALIZER;
+    fill_job job = {seed, first_index, file_len, n_files, out, &next, &mu};
+    pthread_t th[256];
+    int started = 0;
+    for (int t = 0; t < nthreads; t++) {
+        if (pthread_create(&th[t], NULL, fill_worker, &job) != 0) break;
+        started++;
+    }
+    if (!started) fill_worker(&job);
+    for (int t = 0; t < started; t++) pthread_join(th[t], NULL);
+}
+
 /* ------------------------------------------------------------------------------------------
  * Files, the way rclone's local backend hashes them: open, io.Copy through a 32 KiB buffer into
  * the hasher, close -- one file per worker at a time (rclone: 8 checkers, both sides of a pair

@@ -19,7 +19,7 @@ _lib: Optional[C.CDLL] = None
 EXPORTS = [
     "tpimd5_device_count", "tpimd5_init", "tpimd5_destroy", "tpimd5_ctx_devices", "tpimd5_last_error",
     "tpimd5_version", "tpimd5_hash_buffers", "tpimd5_hash_files", "tpimd5_s3_part_size", "tpimd5_s3_nparts",
-    "tpimd5_s3_etag_buffer", "tpimd5_s3_etag_file", "tpimd5_stream_open", "tpimd5_stream_write",
+    "tpimd5_s3_etag_buffer", "tpimd5_s3_etag_file", "tpimd5_s3_plan_parts", "tpimd5_s3_upload_plan", "tpimd5_stream_open", "tpimd5_stream_write",
     "tpimd5_stream_write_many", "tpimd5_stream_sum", "tpimd5_stream_reset", "tpimd5_stream_close", "tpimd5_diff",
     "tpimd5_dev_hash_buffers", "tpimd5_dev_s3_etag", "tpimd5_dev_diff", "tpimd5_dev_synth_fill",
     "tpimd5_dev_s3_etag_noalloc", "tpimd5_filter_new", "tpimd5_filter_free", "tpimd5_filter_include", "tpimd5_filter_include_dir",
@@ -65,6 +65,8 @@ def load_library() -> C.CDLL:
         "tpimd5_s3_nparts": (u32, [u64, u64]),
         "tpimd5_s3_etag_buffer": (i32, [vp, vp, u64, u64, vp, vp, C.POINTER(u32)]),
         "tpimd5_s3_etag_file": (i32, [vp, C.c_char_p, u64, u64, vp, vp, C.POINTER(u32)]),
+        "tpimd5_s3_plan_parts": (u32, [u64, u64, u64, u32, C.POINTER(i32), C.POINTER(u64)]),
+        "tpimd5_s3_upload_plan": (i32, [vp, C.c_char_p, u64, u64, u64, u32, u32, vp, vp, vp]),
         "tpimd5_stream_open": (i32, [vp, C.POINTER(vp)]),
         "tpimd5_stream_write": (i32, [vp, vp, sz]),
         "tpimd5_stream_write_many": (i32, [vp, vp, vp, sz]),
@@ -126,6 +128,21 @@ def s3_part_size(size: int, chunk_size: int = 5 << 20, max_parts: int = 10000) -
 
 def s3_nparts(size: int, part_size: int) -> int:
     return int(load_library().tpimd5_s3_nparts(size, part_size))
+
+
+class _S3Plan(C.Structure):
+    _fields_ = [("multipart", C.c_int32), ("has_md5", C.c_int32), ("part_size", C.c_uint64), ("nparts", C.c_uint32),
+                ("md5", C.c_uint8 * 16), ("content_md5", C.c_char * 25), ("etag", C.c_char * 48)]
+
+
+PLAN_NO_WHOLE_MD5 = 1
+
+
+def s3_plan_parts(size: int, chunk_size: int = 0, upload_cutoff: int = 0, max_parts: int = 0):
+    """rclone's single-vs-multipart decision for an object of `size` bytes -> (multipart, part_size, nparts)."""
+    multi, part = C.c_int32(), C.c_uint64()
+    n = load_library().tpimd5_s3_plan_parts(size, chunk_size, upload_cutoff, max_parts, C.byref(multi), C.byref(part))
+    return bool(multi.value), int(part.value), int(n)
 
 
 def s3_etag_text(etag_md5: bytes, nparts: int) -> str:
@@ -279,6 +296,22 @@ class Context:
         _check(self._L.tpimd5_s3_etag_file(self._h, os.fsencode(path), size, part_size, parts.ctypes.data, etag,
                                            C.byref(npo)))
         return bytes(etag), int(npo.value), parts[: npo.value]
+
+    def s3_upload_plan(self, path: str, size: int, chunk_size: int = 0, upload_cutoff: int = 0, max_parts: int = 0,
+                       no_whole_md5: bool = False) -> dict:
+        """What rclone's S3 back-end computes before uploading `path`: mode, part size, per-part Content-MD5,
+        whole-file Content-MD5 / Md5chksum and the ETag to expect back (tpimd5_s3_upload_plan)."""
+        _, _, n = s3_plan_parts(size, chunk_size, upload_cutoff, max_parts)
+        parts = np.zeros((max(n, 1), 16), dtype=np.uint8)
+        b64 = C.create_string_buffer(25 * max(n, 1))
+        plan = _S3Plan()
+        _check(self._L.tpimd5_s3_upload_plan(self._h, os.fsencode(path), size, chunk_size, upload_cutoff, max_parts,
+                                             PLAN_NO_WHOLE_MD5 if no_whole_md5 else 0, C.byref(plan), parts.ctypes.data, b64))
+        k = int(plan.nparts)
+        return {"multipart": bool(plan.multipart), "part_size": int(plan.part_size), "nparts": k,
+                "md5": bytes(plan.md5) if plan.has_md5 else None,
+                "content_md5": plan.content_md5.decode() if plan.has_md5 else None, "etag": plan.etag.decode(),
+                "part_md5": parts[:k].copy(), "part_content_md5": [b64.raw[25 * i: 25 * i + 24].decode() for i in range(k)]}
 
     def diff(self, old16, new16) -> np.ndarray:
         o, n = _u8(old16), _u8(new16)

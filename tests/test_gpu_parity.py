@@ -261,7 +261,8 @@ def test_full_size_properties_config2():
         assert cnt.item() == 1 and idx[0].item() == victim
 
 
-@pytest.mark.parametrize("variant", [0, 201, 202, 203, 204, 241, 244, 262, 245, 246, 247, 265])
+@pytest.mark.parametrize("variant", [0, 201, 202, 203, 204, 241, 244, 262, 245, 246, 247, 265,
+                                     341, 342, 343, 344, 345, 346, 347, 348, 301, 363])
 def test_tensor_map_kernel_for_strided_units(variant):
     """Equal-sized units at a fixed stride through the TMA kernel: every stride class (multiples of
     16 around the 64/128-byte block and stage boundaries), unit counts that do not fill the last
