@@ -17,8 +17,8 @@
 //     write-after-read ordering is thus carried by the barrier pair, as in any TMA pipeline.
 //   * the 16 message words of block b+1 are fetched from shared memory (4 x LDS.128, un-swizzled
 //     addresses) before block b's 64 steps start: the LDS latency is hidden as well.
-//   * the loop body is two blocks (~9 KiB of SASS): it stays in the instruction caches, unlike an
-//     8-block unrolled stage (37 KiB, beyond the 32 KiB L1.5 I-cache: +14 % per block measured).
+//   * the loop body is U = 2 or 4 blocks (9 or 18 KiB of SASS, inside the 32 KiB L1.5 instruction cache)
+//     and has no branch but its own back edge; all per-stage bookkeeping is unconditional arithmetic.
 //
 // Layout, tensor map and swizzle are those of md5_strided_tma.cuh: unit u = bytes [u*stride,
 // u*stride + unit_len) of one buffer, fresh units only (IV, full padding).
@@ -56,13 +56,14 @@ struct ChainCfg {
     static_assert((NSTAGE & (NSTAGE - 1)) == 0 && (TILES & (TILES - 1)) == 0, "ring arithmetic wants powers of two");
 };
 
-template <int WARPS, int MINB, int NSTAGE, int TILES, int MODE>
+template <int WARPS, int MINB, int NSTAGE, int TILES, int MODE, int U = 2>
 __global__ void __launch_bounds__((WARPS + 1) * 32, MINB)
 md5_chain_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uint32_t unit_len, uint4 *__restrict__ table) {
     using Cfg = ChainCfg<WARPS, NSTAGE, TILES>;
     constexpr uint32_t SB = 128u * TILES;                      // bytes of one unit per stage
     constexpr uint32_t BPS = 2u * TILES;                       // MD5 blocks per stage
     constexpr uint32_t RB = BPS * NSTAGE;                      // blocks in the whole ring of a warp
+    static_assert((U == 2 || U == 4) && (uint32_t)U <= BPS, "an iteration must not span stages");
     extern __shared__ uint8_t smem_raw[];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);     // warp-uniform by construction
@@ -74,7 +75,7 @@ md5_chain_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uint3
 #pragma unroll
         for (int i = 0; i < WARPS * NSTAGE; ++i) {
             mbar_init(bars + 8u * i, 1);                                  // full: the producer's expect_tx arrival
-            mbar_init(bars + 8u * (WARPS * NSTAGE + i), TILES);           // empty: one arrival per box read
+            mbar_init(bars + 8u * (WARPS * NSTAGE + i), BPS / U);         // empty: one arrival per loop iteration
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -145,44 +146,57 @@ md5_chain_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uint3
         wait_stage(0);
         lds16(mA, xa, 0u);
     }
-    // Main loop: two whole blocks per iteration, b (even, already in mA) and b+1 (same box, fetched into mB
-    // now), while a further whole block b+2 exists to be prefetched.  Nothing in the body is conditional
-    // except the (never taken) spin when the next stage has not landed:
-    //  - the "full" barrier of block b+2's stage is polled EVERY iteration -- within a stage it has long
-    //    completed and the poll is free; at a stage boundary its latency runs under block b's 64 steps;
+    // Main loop: U whole blocks per iteration (b .. b+U-1; b already in mA), while a further whole block
+    // b+U exists to be prefetched.  Two register sets alternate, each block's words fetched under the
+    // 64 steps of the block before it.  Nothing in the body is conditional except the (never taken)
+    // spin when the next stage has not landed:
+    //  - the "full" barrier of block b+U's stage is polled EVERY iteration -- within a stage it has long
+    //    completed and the poll is free; at a stage boundary its latency runs under the iteration's steps;
     //  - lane 0 arrives on the "empty" barrier of the current stage EVERY iteration; the barrier counts
-    //    TILES arrivals (one per box), so it completes exactly when the stage has been read.
+    //    BPS/U arrivals, so it completes exactly when the stage has been read.
     constexpr uint32_t LOG_BPS = TILES == 1 ? 1 : TILES == 2 ? 2 : TILES == 4 ? 3 : 4;
     constexpr uint32_t LOG_NST = NSTAGE == 1 ? 0 : NSTAGE == 2 ? 1 : NSTAGE == 4 ? 2 : 3;
     constexpr uint32_t RING_MASK = (RB / 2u) * 4096u - 1u;     // boxes of the ring, in bytes
     uint32_t box = 0;                                          // byte offset of block b's box in the ring
-    if (bm > 2u) {
+    if (bm > (uint32_t)U) {
         bool again;
         do {
-            const uint32_t s2 = (b + 2u) >> LOG_BPS;           // stage of block b+2
+            const uint32_t s2 = (b + U) >> LOG_BPS;            // stage of block b+U
             const uint32_t landed = mbar_try_wait(full0 + ((s2 & (NSTAGE - 1u)) << 3), (s2 >> LOG_NST) & 1u);
-            lds16(mB, xb, box);
-            again = b + 4u < bm;
-            md5_block<MODE>(st, mA);
-            if (!landed) wait_stage(s2);
-            const uint32_t box2 = (box + 4096u) & RING_MASK;
-            lds16(mA, xa, box2);
-            md5_block<MODE>(st, mB);
-            __syncwarp();                                      // all 32 rows of this box are in registers (and consumed)
+            again = b + 2u * U < bm;
+            const uint32_t box_next = (box + (U / 2u) * 4096u) & RING_MASK;
+#pragma unroll
+            for (int j = 0; j < U; j += 2) {
+                lds16(mB, xb, box + (uint32_t)(j / 2) * 4096u);             // block b+j+1: same box as b+j
+                md5_block<MODE>(st, mA);                                    // block b+j
+                if (j + 2 < U) {
+                    lds16(mA, xa, box + (uint32_t)(j / 2 + 1) * 4096u);     // block b+j+2: next box of this stage
+                } else {
+                    if (!landed) wait_stage(s2);
+                    lds16(mA, xa, box_next);                                // block b+U
+                }
+                md5_block<MODE>(st, mB);                                    // block b+j+1
+            }
+            __syncwarp();                                      // all 32 rows of these boxes are in registers (and consumed)
             if (lane == 0) mbar_arrive(empty0 + (((b >> LOG_BPS) & (NSTAGE - 1u)) << 3));
-            b += 2u;
-            box = box2;
+            b += U;
+            box = box_next;
         } while (again);
     }
-    // at most two whole blocks are left: b (in mA) and b+1
-    if (b + 1u < bm) {
-        lds16(mB, xb, box);
-        md5_block<MODE>(st, mA);
-        md5_block<MODE>(st, mB);
-        b += 2u;
-    } else if (b < bm) {
+    // up to U whole blocks are left; b is in mA.  (xb[q] == xa[q] ^ 64: the other half of the row.)
+    while (b < bm) {
         md5_block<MODE>(st, mA);
         ++b;
+        if (b < bm) {
+            wait_stage(b / BPS);                               // returns at once for a stage already waited for
+            const uint32_t bx = box_of(b), half = (b & 1u) << 6;
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                             : "=r"(mA[4 * q]), "=r"(mA[4 * q + 1]), "=r"(mA[4 * q + 2]), "=r"(mA[4 * q + 3])
+                             : "r"((xa[q] ^ half) + bx)
+                             : "memory");
+        }
     }
 
     // ---- the block that takes the 0x80 marker, and the length block if the 8 length bytes do not fit ----

@@ -331,7 +331,7 @@ extern "C" void tpimd5_destroy(tpimd5_ctx *ctx) {
 extern "C" int tpimd5_ctx_devices(const tpimd5_ctx *ctx) { return ctx ? (int)ctx->slots.size() : 0; }
 extern "C" uint64_t tpimd5_launch_count(const tpimd5_ctx *ctx) { return ctx ? ctx->launches.load() : 0; }
 extern "C" int tpimd5_set_variant(tpimd5_ctx *ctx, int variant) {
-    if (!ctx || variant < 0 || variant > 399) return fail(TPIMD5_EINVAL, "tpimd5_set_variant: 100*loader(0 cp.async, 2 tensor map for strided units, 3 latency kernel for strided units) + 10*mode(0,4,6) + shape");
+    if (!ctx || variant < 0 || variant > 499) return fail(TPIMD5_EINVAL, "tpimd5_set_variant: 100*loader(0 cp.async, 2 tensor map for strided units, 3 / 4 latency kernel for strided units, 2 / 4 blocks per iteration) + 10*mode(0,4,6) + shape");
     ctx->variant = variant;
     return 0;
 }
@@ -439,10 +439,10 @@ static int launch_tma_cfg(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len
     return 0;
 }
 
-template <int WARPS, int MINB, int NSTAGE, int TILES, int MODE>
+template <int WARPS, int MINB, int NSTAGE, int TILES, int MODE, int U = 2>
 static int launch_chain_cfg(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len, uint4 *table, cudaStream_t st) {
     using Cfg = ChainCfg<WARPS, NSTAGE, TILES>;
-    auto kern = md5_chain_tma_kernel<WARPS, MINB, NSTAGE, TILES, MODE>;
+    auto kern = md5_chain_tma_kernel<WARPS, MINB, NSTAGE, TILES, MODE, U>;
     static ConfiguredSet configured;
     int dev = 0;
     CU(cudaGetDevice(&dev));
@@ -458,19 +458,22 @@ static int launch_chain_cfg(const CUtensorMap &tmap, uint64_t n, uint32_t unit_l
     return 0;
 }
 
-// The latency kernel (md5_chain_tma.cuh) in one of its shapes; mode 4 unless 0 or 6 is asked for.
+// The latency kernel (md5_chain_tma.cuh) in one of its shapes; mode 4 unless 0 or 6 is asked for; U blocks
+// per loop iteration.
+template <int U>
 static int launch_chain(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len, uint4 *table, int shape, int mode, cudaStream_t st) {
-#define TPI_CHAIN(M)                                                                           \
-    switch (shape) {                                                                           \
-        default:                                                                               \
-        case 1: return launch_chain_cfg<4, 1, 2, 4, M>(tmap, n, unit_len, table, st);          \
-        case 2: return launch_chain_cfg<4, 1, 4, 2, M>(tmap, n, unit_len, table, st);          \
-        case 3: return launch_chain_cfg<4, 3, 2, 2, M>(tmap, n, unit_len, table, st);          \
-        case 4: return launch_chain_cfg<4, 3, 4, 1, M>(tmap, n, unit_len, table, st);          \
-        case 5: return launch_chain_cfg<4, 6, 2, 1, M>(tmap, n, unit_len, table, st);          \
-        case 6: return launch_chain_cfg<2, 2, 4, 2, M>(tmap, n, unit_len, table, st);          \
-        case 7: return launch_chain_cfg<4, 1, 8, 1, M>(tmap, n, unit_len, table, st);          \
-        case 8: return launch_chain_cfg<2, 4, 2, 2, M>(tmap, n, unit_len, table, st);          \
+#define TPI_CHAIN(M)                                                                              \
+    switch (shape) {                                                                              \
+        default:                                                                                  \
+        case 1: return launch_chain_cfg<4, 1, 2, 4, M, U>(tmap, n, unit_len, table, st);          \
+        case 2: return launch_chain_cfg<4, 1, 4, 2, M, U>(tmap, n, unit_len, table, st);          \
+        case 3: return launch_chain_cfg<4, 3, 2, 2, M, U>(tmap, n, unit_len, table, st);          \
+        case 4: return launch_chain_cfg<4, 5, 2, 1, M, 2>(tmap, n, unit_len, table, st);          \
+        case 5: return launch_chain_cfg<4, 6, 2, 1, M, 2>(tmap, n, unit_len, table, st);          \
+        case 6: return launch_chain_cfg<2, 2, 4, 2, M, U>(tmap, n, unit_len, table, st);          \
+        case 7: return launch_chain_cfg<8, 3, 2, 1, M, 2>(tmap, n, unit_len, table, st);          \
+        case 8: return launch_chain_cfg<2, 4, 2, 2, M, U>(tmap, n, unit_len, table, st);          \
+        case 9: return launch_chain_cfg<3, 1, 2, 4, M, U>(tmap, n, unit_len, table, st);          \
     }
     if (mode == 0) { TPI_CHAIN(0) }
     if (mode == 6) { TPI_CHAIN(6) }
@@ -491,8 +494,9 @@ static int launch_strided_tma(tpimd5_ctx *ctx, const void *base, uint64_t stride
                                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(TPIMD5_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
     int rc;
-    if (loader == 3) {
-        rc = launch_chain(tmap, n, (uint32_t)unit_len, table, shape, mode, st);
+    if (loader >= 3) {
+        rc = loader == 3 ? launch_chain<2>(tmap, n, (uint32_t)unit_len, table, shape, mode, st)
+                         : launch_chain<4>(tmap, n, (uint32_t)unit_len, table, shape, mode, st);
         if (rc == 0) ctx->launches.fetch_add(1);
         return rc;
     }
@@ -500,19 +504,21 @@ static int launch_strided_tma(tpimd5_ctx *ctx, const void *base, uint64_t stride
     // the latency kernel (md5_chain_tma.cuh; mode 4 = LOP3 -> IADD3 -> LEA.HI, the shortest chain), in the
     // shape that spreads its warps thinnest over the SM sub-partitions (measured, profiles/r2_chain_sweep.md):
     //   <= 148 warps             2 hashing warps per CTA, <= 74 CTAs: one warp per sub-partition, and two
-    //                            such launches still fit side by side (two S3 files on two streams)
-    //   <= 592 warps             4 hashing warps per CTA, one CTA per SM (128 KiB of stages each)
-    //   <= 888 warps             2 per CTA, up to three CTAs per SM: at most two warps per sub-partition
+    //                            such launches still fit side by side
+    //   <= 592 warps             4 hashing warps per CTA, one CTA per SM (128 KiB of stages each); two
+    //                            launches of one 64 GiB S3 object each (2 x 64 CTAs) still get an SM per CTA
+    //   <= 888 warps             3 per CTA (+ the producer: one warp per sub-partition), up to two CTAs per SM
     //   <= 1,776 warps           4 per CTA, up to three CTAs per SM; three warps share a sub-partition, where
     //                            the integer pipes start to bind: the step formulation that splits the adds (6)
     // Beyond that (12 warps per SM would no longer hold the launch in one wave) the throughput kernel below.
+    // All with four blocks per loop iteration.
     const uint64_t warps = (n + 31) / 32;
     if (shape == 0 && warps <= (uint64_t)148 * 12) {
         const uint32_t ul = (uint32_t)unit_len;
-        if (warps <= 148) rc = launch_chain_cfg<2, 2, 4, 2, 4>(tmap, n, ul, table, st);
-        else if (warps <= 592) rc = launch_chain_cfg<4, 1, 2, 4, 4>(tmap, n, ul, table, st);
-        else if (warps <= 888) rc = launch_chain_cfg<2, 2, 4, 2, 4>(tmap, n, ul, table, st);
-        else rc = launch_chain_cfg<4, 3, 2, 2, 6>(tmap, n, ul, table, st);
+        if (warps <= 148) rc = launch_chain_cfg<2, 2, 4, 2, 4, 4>(tmap, n, ul, table, st);
+        else if (warps <= 592) rc = launch_chain_cfg<4, 1, 2, 4, 4, 4>(tmap, n, ul, table, st);
+        else if (warps <= 888) rc = launch_chain_cfg<3, 1, 2, 4, 4, 4>(tmap, n, ul, table, st);
+        else rc = launch_chain_cfg<4, 3, 2, 2, 6, 4>(tmap, n, ul, table, st);
         if (rc == 0) ctx->launches.fetch_add(1);
         return rc;
     }
