@@ -569,11 +569,25 @@ def run_c4(env):
     total = int(off[-1] + mine[-1])
     data = torch.empty((total + 15) // 16 * 16, dtype=torch.uint8, device=dev)
     ctx.dev_synth_fill(data, 4, env.rank, 16, data.numel() // 16, stream=env.stream)
-    d_off, d_len = torch.from_numpy(off).to(dev), torch.from_numpy(mine).to(dev)
+    # the caller knows the listing: files of 8 MiB and more go in as single strided units on streams of their
+    # own (the latency kernel, fed by TMA; a unit longer than a tensor-map row continues across launches),
+    # everything else as one ragged batch
+    big = np.nonzero(mine >= (8 << 20))[0]
+    small = np.nonzero(mine < (8 << 20))[0]
+    d_off, d_len = torch.from_numpy(off[small]).to(dev), torch.from_numpy(mine[small]).to(dev)
     dig = torch.empty((mine.size, 16), dtype=torch.uint8, device=dev)
+    dig_small = torch.empty((small.size, 16), dtype=torch.uint8, device=dev)
+    side = [torch.cuda.Stream(device=dev) for _ in big]
 
     def step():
-        ctx.dev_hash_buffers(data, total, mine.size, dig, d_offsets=d_off, d_lengths=d_len, stream=env.stream)
+        cur = torch.cuda.current_stream()
+        for st_, i in zip(side, big.tolist()):
+            st_.wait_stream(cur)
+            ln = int(mine[i])
+            ctx.dev_hash_buffers(data[int(off[i]):], ln, 1, dig[i:i + 1], stride=(ln + 15) // 16 * 16, stream=st_.cuda_stream)
+        ctx.dev_hash_buffers(data, total, small.size, dig_small, d_offsets=d_off, d_lengths=d_len, stream=env.stream)
+        for st_ in side:
+            cur.wait_stream(st_)
 
     ms, ms_local, clocks, launches = env.timed(step, 1, 1)
     work_bytes = int(sizes.sum())

@@ -21,7 +21,8 @@
 //     and has no branch but its own back edge; all per-stage bookkeeping is unconditional arithmetic.
 //
 // Layout, tensor map and swizzle are those of md5_strided_tma.cuh: unit u = bytes [u*stride,
-// u*stride + unit_len) of one buffer, fresh units only (IV, full padding).
+// u*stride + unit_len) of one buffer.  Units of any length: a launch hashes at most 2^30 bytes of each
+// (one tensor-map row) and long units continue from launch to launch through the digest table.
 #pragma once
 #include <cuda.h>
 
@@ -58,7 +59,8 @@ struct ChainCfg {
 
 template <int WARPS, int MINB, int NSTAGE, int TILES, int MODE, int U = 2>
 __global__ void __launch_bounds__((WARPS + 1) * 32, MINB)
-md5_chain_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uint32_t unit_len, uint4 *__restrict__ table) {
+md5_chain_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uint32_t unit_len, uint4 *__restrict__ table,
+                     uint64_t prior, uint32_t flags) {
     using Cfg = ChainCfg<WARPS, NSTAGE, TILES>;
     constexpr uint32_t SB = 128u * TILES;                      // bytes of one unit per stage
     constexpr uint32_t BPS = 2u * TILES;                       // MD5 blocks per stage
@@ -138,8 +140,17 @@ md5_chain_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uint3
     };
     auto full_bar = [&](uint32_t S) { return full0 + 8u * (S & (NSTAGE - 1u)); };
     auto wait_stage = [&](uint32_t S) { mbar_wait(full_bar(S), (S / NSTAGE) & 1u); };
+    // A unit longer than one launch may carry (a tensor-map row is at most 2^31 bytes) is hashed as a
+    // run of launches: all but the first start from the chaining value the previous one left in the
+    // table (LANE_CONT, `prior` bytes already hashed), all but the last store the chaining value
+    // instead of finalising (no LANE_FINAL; their unit_len is a multiple of 64).
     uint32_t st[4];
-    md5_iv(st);
+    if ((flags & LANE_CONT) && u < n) {
+        const uint4 v = table[u];
+        st[0] = v.x; st[1] = v.y; st[2] = v.z; st[3] = v.w;
+    } else {
+        md5_iv(st);
+    }
     uint32_t mA[16], mB[16];
     uint32_t b = 0;
     if (bm >= 1u) {
@@ -200,7 +211,8 @@ md5_chain_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uint3
     }
 
     // ---- the block that takes the 0x80 marker, and the length block if the 8 length bytes do not fit ----
-    {
+    if (flags & LANE_FINAL) {
+        const uint64_t total = prior + unit_len;
         uint32_t m[16];
         if (rem) {
             wait_stage(bm / BPS);                              // returns at once if this stage was waited for before
@@ -210,12 +222,12 @@ md5_chain_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uint3
 #pragma unroll
             for (int q = 0; q < 16; ++q) m[q] = 0;
         }
-        md5_pad_block(m, rem, false, (uint64_t)unit_len);
+        md5_pad_block(m, rem, false, total);
         md5_block<MODE>(st, m);
         if (nb > bm + 1u) {
 #pragma unroll
             for (int q = 0; q < 16; ++q) m[q] = 0;
-            md5_pad_block(m, rem, true, (uint64_t)unit_len);
+            md5_pad_block(m, rem, true, total);
             md5_block<MODE>(st, m);
         }
     }

@@ -207,6 +207,9 @@ struct tpimd5_ctx {
     size_t staging = DEFAULT_STAGING;
     std::atomic<uint64_t> launches{0};
     std::atomic<int> variant{0};
+    // longest tensor-map row, and bytes of a longer unit hashed per launch (tests shrink both through the
+    // environment to run the segment logic on small data)
+    uint64_t row_max = (uint64_t)1 << 31, chain_seg = (uint64_t)1 << 30;
 };
 
 static constexpr size_t desc_bytes_per_lane = 3 * sizeof(uint64_t) + 2 * sizeof(uint32_t);
@@ -293,6 +296,14 @@ extern "C" int tpimd5_init(const int *device_ids, int n_devices, size_t staging_
         CU(cudaStreamCreateWithFlags(&s->s_comp, cudaStreamNonBlocking));
         for (int b = 0; b < NBUF; ++b) CU(cudaStreamCreateWithFlags(&s->s_batch[b], cudaStreamNonBlocking));
         ctx->slots.push_back(std::move(s));
+    }
+    if (const char *e = getenv("TPIMD5_ROW_MAX")) {
+        const uint64_t v = strtoull(e, nullptr, 0);
+        if (v >= 64 && v <= ((uint64_t)1 << 31)) ctx->row_max = v;
+    }
+    if (const char *e = getenv("TPIMD5_CHAIN_SEG")) {
+        const uint64_t v = strtoull(e, nullptr, 0);
+        if (v >= 64 && v <= ((uint64_t)1 << 30) && v % 64 == 0) ctx->chain_seg = v;
     }
     unsigned hc = std::thread::hardware_concurrency();
     int workers = (int)std::min<unsigned>(hc ? hc : 4, 32);
@@ -414,12 +425,12 @@ static EncodeTiledFn encode_tiled_fn() {
     return fn;
 }
 
-// Can this strided launch go through the tensor-map kernel?
-static bool tma_eligible(const void *base, uint64_t stride, uint64_t unit_len, uint64_t n) {
-    return ((uintptr_t)base & 15) == 0 && (stride & 15) == 0 && stride < ((uint64_t)1 << 40) && unit_len >= 1 &&
-           unit_len <= stride && unit_len <= ((uint64_t)1 << 31) && n >= 1 && n <= ((uint64_t)1 << 31) && encode_tiled_fn() != nullptr;
+// Can this strided layout be described to the TMA unit?  (A row longer than 2^31 bytes cannot; such units
+// are hashed in segments, see launch_long_units.)
+static bool tma_layout_ok(const void *base, uint64_t stride, uint64_t n) {
+    return ((uintptr_t)base & 15) == 0 && (stride & 15) == 0 && stride >= 16 && stride < ((uint64_t)1 << 40) && n >= 1 &&
+           n <= ((uint64_t)1 << 31) && encode_tiled_fn() != nullptr;
 }
-
 template <int WARPS, int MINB, int NSTAGE, int MODE, int TILES = 1>
 static int launch_tma_cfg(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len, uint4 *table, cudaStream_t st) {
     using Cfg = StridedCfg<WARPS, NSTAGE, TILES>;
@@ -440,7 +451,8 @@ static int launch_tma_cfg(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len
 }
 
 template <int WARPS, int MINB, int NSTAGE, int TILES, int MODE, int U = 2>
-static int launch_chain_cfg(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len, uint4 *table, cudaStream_t st) {
+static int launch_chain_cfg(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len, uint4 *table, cudaStream_t st,
+                            uint64_t prior = 0, uint32_t flags = LANE_FINAL) {
     using Cfg = ChainCfg<WARPS, NSTAGE, TILES>;
     auto kern = md5_chain_tma_kernel<WARPS, MINB, NSTAGE, TILES, MODE, U>;
     static ConfiguredSet configured;
@@ -453,7 +465,7 @@ static int launch_chain_cfg(const CUtensorMap &tmap, uint64_t n, uint32_t unit_l
     }
     const uint64_t per_cta = WARPS * 32;
     const uint64_t grid = (n + per_cta - 1) / per_cta;
-    kern<<<(unsigned)grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(tmap, n, unit_len, table);
+    kern<<<(unsigned)grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(tmap, n, unit_len, table, prior, flags);
     CU(cudaGetLastError());
     return 0;
 }
@@ -481,18 +493,53 @@ static int launch_chain(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len, 
 #undef TPI_CHAIN
 }
 
+// Does a launch of n units fit the latency kernel in one wave (at most 12 hashing warps per SM)?
+static bool chain_launch_fits(uint64_t n) { return (n + 31) / 32 <= (uint64_t)148 * 12; }
+
+// The latency kernel in the shape that suits the launch's warp count (see launch_strided_tma).
+static int launch_chain_default(const CUtensorMap &tmap, uint64_t n, uint32_t ul, uint4 *table, cudaStream_t st, uint64_t prior,
+                                uint32_t flags) {
+    const uint64_t warps = (n + 31) / 32;
+    if (warps <= 148) return launch_chain_cfg<2, 2, 4, 2, 4, 4>(tmap, n, ul, table, st, prior, flags);
+    if (warps <= 592) return launch_chain_cfg<4, 1, 2, 4, 4, 4>(tmap, n, ul, table, st, prior, flags);
+    if (warps <= 888) return launch_chain_cfg<3, 1, 2, 4, 4, 4>(tmap, n, ul, table, st, prior, flags);
+    return launch_chain_cfg<4, 3, 2, 2, 6, 4>(tmap, n, ul, table, st, prior, flags);
+}
+
+static int encode_rows(CUtensorMap *tmap, const void *base, uint64_t row_bytes, uint64_t rows, uint64_t pitch) {
+    const cuuint64_t gdim[2] = {row_bytes, rows};
+    const cuuint64_t gstride[1] = {pitch};
+    const cuuint32_t box[2] = {128, 32};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult r = encode_tiled_fn()(tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(base), gdim, gstride, box, estr,
+                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(TPIMD5_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return 0;
+}
+
+// Units too long for one tensor-map row (large files: C4's 32 GiB object): CHAIN_SEG bytes of every unit
+// per launch, the chaining values carried from launch to launch in the digest table.
+static int launch_long_units(tpimd5_ctx *ctx, const void *base, uint64_t stride, uint64_t unit_len, uint64_t n, uint4 *table,
+                             cudaStream_t st) {
+    for (uint64_t done = 0; done < unit_len; done += ctx->chain_seg) {
+        const uint64_t seg = std::min(ctx->chain_seg, unit_len - done);
+        CUtensorMap tmap;
+        int rc = encode_rows(&tmap, (const uint8_t *)base + done, seg, n, stride);
+        if (rc) return rc;
+        const uint32_t flags = (done ? LANE_CONT : 0u) | (done + seg == unit_len ? LANE_FINAL : 0u);
+        rc = launch_chain_default(tmap, n, (uint32_t)seg, table, st, done, flags);
+        if (rc) return rc;
+        ctx->launches.fetch_add(1);
+    }
+    return 0;
+}
+
 // n units of unit_len bytes, unit u at base + u*stride.  shape: 1..4, mode 0 or 4.
 static int launch_strided_tma(tpimd5_ctx *ctx, const void *base, uint64_t stride, uint64_t unit_len, uint64_t n, uint4 *table,
                               int loader, int shape, int mode, cudaStream_t st) {
     CUtensorMap tmap;
-    const cuuint64_t gdim[2] = {unit_len, n};
-    const cuuint64_t gstride[1] = {stride};
-    const cuuint32_t box[2] = {128, 32};
-    const cuuint32_t estr[2] = {1, 1};
-    CUresult r = encode_tiled_fn()(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(base), gdim, gstride, box, estr,
-                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return fail(TPIMD5_ECUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    if (int rc0 = encode_rows(&tmap, base, unit_len, n, stride)) return rc0;
     int rc;
     if (loader >= 3) {
         rc = loader == 3 ? launch_chain<2>(tmap, n, (uint32_t)unit_len, table, shape, mode, st)
@@ -512,13 +559,8 @@ static int launch_strided_tma(tpimd5_ctx *ctx, const void *base, uint64_t stride
     //                            the integer pipes start to bind: the step formulation that splits the adds (6)
     // Beyond that (12 warps per SM would no longer hold the launch in one wave) the throughput kernel below.
     // All with four blocks per loop iteration.
-    const uint64_t warps = (n + 31) / 32;
-    if (shape == 0 && warps <= (uint64_t)148 * 12) {
-        const uint32_t ul = (uint32_t)unit_len;
-        if (warps <= 148) rc = launch_chain_cfg<2, 2, 4, 2, 4, 4>(tmap, n, ul, table, st);
-        else if (warps <= 592) rc = launch_chain_cfg<4, 1, 2, 4, 4, 4>(tmap, n, ul, table, st);
-        else if (warps <= 888) rc = launch_chain_cfg<3, 1, 2, 4, 4, 4>(tmap, n, ul, table, st);
-        else rc = launch_chain_cfg<4, 3, 2, 2, 6, 4>(tmap, n, ul, table, st);
+    if (shape == 0 && chain_launch_fits(n)) {
+        rc = launch_chain_default(tmap, n, (uint32_t)unit_len, table, st, 0, LANE_FINAL);
         if (rc == 0) ctx->launches.fetch_add(1);
         return rc;
     }
@@ -591,11 +633,21 @@ static int launch_strided(tpimd5_ctx *ctx, const void *base, uint64_t base_bytes
     int loader, mode, shape;
     decode_variant(ctx->variant.load(), loader, mode, shape);
     const uint64_t n_full = std::min<uint64_t>(n, base_bytes / stride);
-    if (loader >= 2 && n_full && tma_eligible(base, stride, stride, n_full)) {
-        int rc = launch_strided_tma(ctx, base, stride, stride, n_full, table, loader, shape, mode, st);
+    if (loader >= 2 && n_full && tma_layout_ok(base, stride, n_full) && (stride <= ctx->row_max || chain_launch_fits(n_full))) {
+        int rc = stride <= ctx->row_max ? launch_strided_tma(ctx, base, stride, stride, n_full, table, loader, shape, mode, st)
+                                       : launch_long_units(ctx, base, stride, stride, n_full, table, st);
         if (rc || n_full == n) return rc;
         a.base += n_full * stride; a.base_bytes -= n_full * stride; a.table += n_full; a.n = n - n_full;
     }
+    // what is left is units that the buffer's end cuts short: one ragged unit (then possibly empty ones)
+    if (loader >= 2 && a.n == 1 && a.base_bytes >= 16 && tma_layout_ok(a.base, stride, 1)) {
+        const uint64_t pitch = (a.base_bytes + 15) & ~(uint64_t)15;       // one row: the pitch is never applied
+        return a.base_bytes <= ctx->row_max ? launch_strided_tma(ctx, a.base, pitch, a.base_bytes, 1, a.table, loader, shape, mode, st)
+                                           : launch_long_units(ctx, a.base, pitch, a.base_bytes, 1, a.table, st);
+    }
+    if (a.base_bytes > MAX_LANE_BYTES && a.stride > MAX_LANE_BYTES)
+        return fail(TPIMD5_ERANGE, "a unit above %llu bytes must start on a 16-byte boundary and have a stride that is a multiple of 16",
+                    (unsigned long long)MAX_LANE_BYTES);
     return launch_lanes(ctx, a, aligned, st);
 }
 
@@ -621,7 +673,6 @@ extern "C" int tpimd5_dev_hash_buffers(tpimd5_ctx *ctx, int slot, const void *d_
         aligned = false;  // offsets live on the device; the general kernel takes any alignment
     } else {
         if (stride == 0) return fail(TPIMD5_EINVAL, "dev_hash_buffers: stride 0");
-        if (stride > MAX_LANE_BYTES) return fail(TPIMD5_ERANGE, "dev_hash_buffers: unit above %llu bytes", (unsigned long long)MAX_LANE_BYTES);
         if ((n - 1) > base_bytes / stride) return fail(TPIMD5_EINVAL, "dev_hash_buffers: n*stride runs past base_bytes");
         aligned = ((uintptr_t)d_base & 15) == 0 && (stride & 15) == 0;
     }
@@ -681,7 +732,6 @@ extern "C" int tpimd5_dev_s3_etag(tpimd5_ctx *ctx, int slot, const void *d_data,
     if (!s) return fail(TPIMD5_EINVAL, "dev_s3_etag: bad context or slot");
     if (!d_etag_md5_out || (!d_data && size)) return fail(TPIMD5_EINVAL, "dev_s3_etag: null pointer");
     if (part_size == 0) return fail(TPIMD5_EINVAL, "dev_s3_etag: part_size 0");
-    if (part_size > MAX_LANE_BYTES) return fail(TPIMD5_ERANGE, "dev_s3_etag: part above %llu bytes", (unsigned long long)MAX_LANE_BYTES);
     const uint32_t np = tpimd5_s3_nparts(size, part_size);
     if (!np) return fail(TPIMD5_ERANGE, "dev_s3_etag: too many parts");
     USE_DEVICE(s->dev);
