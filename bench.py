@@ -698,13 +698,14 @@ def run_c2_files(env, n=200_000):
                 os.close(fd)
         with ThreadPoolExecutor(8) as ex:
             list(ex.map(lambda lo: write_range(lo, min(n, lo + 4096)), range(0, n, 4096)))
-        sizes = [FILE_BYTES] * n
+        sizes = np.full(n, FILE_BYTES, dtype=np.uint64)
+        listing = env.tpi.PathList(paths)          # the listing as C strings, encoded once (both arms use it)
         l0 = ctx.launch_count()
-        ctx.hash_files(paths[:2000], sizes[:2000])
+        ctx.hash_files(listing, sizes)             # warm: staging buffers are allocated on first use
         t = []
         for _ in range(3):
             t0 = time.perf_counter()
-            got = ctx.hash_files(paths, sizes)
+            got = ctx.hash_files(listing, sizes)
             t.append(time.perf_counter() - t0)
         launches = int(ctx.launch_count() - l0)
         eng, kind = cpu_engine()
@@ -713,7 +714,7 @@ def run_c2_files(env, n=200_000):
         tc = []
         for _ in range(3):
             t0 = time.perf_counter()
-            want = oracle.md5_files(paths, threads, eng)
+            want = oracle.md5_files(listing, threads, eng)
             tc.append(time.perf_counter() - t0)
         if not np.array_equal(got, want):
             raise SystemExit("bench.py: c2_files digests differ from the CPU path's")

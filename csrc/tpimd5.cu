@@ -14,6 +14,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cerrno>
+#include <chrono>
 #include <condition_variable>
 #include <cstdarg>
 #include <cstdio>
@@ -23,7 +24,9 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <sched.h>
 #include <sys/stat.h>
+#include <sys/syscall.h>
 #include <thread>
 #include <unistd.h>
 #include <vector>
@@ -145,7 +148,21 @@ class Pool {
         std::lock_guard<std::mutex> g(j.mu);
         if (--j.pending == 0) j.cv.notify_all();
     }
+    // Reader threads get a file-descriptor table of their own.  open() and close() serialise on a lock of the
+    // table, which all threads of a process normally share: 16 threads reading 4 KiB files reach 1.5 M files/s
+    // with the shared table and well beyond with private ones (tools/smallfile_bench.cc).  unshare(CLONE_FILES)
+    // gives the thread a COPY of the table, so every inherited descriptor is closed in that copy at once --
+    // otherwise the copies would keep the caller's sockets and deleted files alive.  These threads only ever
+    // open, read and close the files they are given (and memcpy); they never call CUDA.
+    static void private_fd_table() {
+        const char *off = getenv("TPIMD5_SHARED_FDS");
+        if (off && off[0] == '1') return;
+        if (syscall(SYS_close_range, 1u, 0u, 0u) != -1 || errno != EINVAL) return;   // first > last: EINVAL iff the call exists
+        if (unshare(CLONE_FILES) != 0) return;
+        syscall(SYS_close_range, 0u, ~0u, 0u);
+    }
     void run() {
+        private_fd_table();
         for (;;) {
             std::shared_ptr<Job> job;
             {
@@ -168,7 +185,7 @@ class Pool {
 // ------------------------------------------------------------------------------------------------
 // context
 // ------------------------------------------------------------------------------------------------
-constexpr int NBUF = 8;                       // staging buffers (and batch kernels) in flight per device, allocated as needed:
+constexpr int NBUF = 12;                      // staging buffers (and batch kernels) in flight per device, allocated as needed:
                                               // bytes in flight / time of the longest chain bounds ingest of large files
 constexpr size_t MAX_BATCH_LANES = 1u << 20;  // descriptor rows per staging buffer
 constexpr size_t DEFAULT_STAGING = 256u << 20;   // measured best for C1/C2 end to end; 512 MiB is better for multi-GiB files (see tpimd5_init)
@@ -914,9 +931,20 @@ static int read_fully(int fd, uint8_t *dst, uint64_t off, uint64_t n, bool probe
     return 0;
 }
 
+// TPIMD5_TRACE=1: phase timings of the ingest pipeline on stderr (diagnostics only)
+static bool trace_on() {
+    static const bool on = [] { const char *e = getenv("TPIMD5_TRACE"); return e && e[0] == '1'; }();
+    return on;
+}
+static double trace_now() {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
 // Runs one device's share of a job.  `units` are indices into the job.
 static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint32_t> &units_in) {
     if (units_in.empty()) return 0;
+    const double tr0 = trace_now();
+    double tr_plan = 0, tr_fill = 0, tr_wait = 0;
     // Files: longest first.  One file is one serial chain (~125 MB/s), so the device's finish time is
     // bounded by its longest file; starting those in the first batch lets the short ones fill in behind.
     std::vector<uint32_t> by_size;
@@ -965,6 +993,8 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
         }
     }
 
+    int tma_loader, tma_mode, tma_shape;
+    decode_variant(ctx->variant.load(), tma_loader, tma_mode, tma_shape);
     std::vector<Piece> pieces;
     std::vector<uint32_t> order;
     size_t ui = 0;            // next unit
@@ -977,6 +1007,7 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
         const int bi = batch % NBUF;
         rc = ensure_buffer(ctx, s, bi, !direct);
         if (rc) return rc;
+        const double tr_b0 = trace_now();
         // ---- plan one batch --------------------------------------------------------------------
         pieces.clear();
         uint64_t used = 0;       // bytes of staging consumed
@@ -1014,7 +1045,10 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
         const size_t np = pieces.size();
 
         // ---- wait until this staging buffer's previous batch has been consumed -----------------
+        const double tr_b1 = trace_now();
         if (batch >= NBUF) CU(cudaEventSynchronize(s.ev_done[bi]));
+        tr_plan += tr_b1 - tr_b0;
+        tr_wait += trace_now() - tr_b1;
 
         // ---- lanes, longest first so that a warp's 32 units finish together ---------------------
         order.resize(np);
@@ -1031,9 +1065,25 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
             aligned = aligned && (pieces[i].dst & 15) == 0;
             if (pieces[i].len > MAX_LANE_BYTES) return fail(TPIMD5_ERANGE, "staging above %llu bytes per unit is not supported", (unsigned long long)MAX_LANE_BYTES);
         }
+        // A batch of whole, fresh units of one length at one spacing (a workdir of equal small files, the parts of
+        // one S3 object) needs no per-unit descriptors at all: it is described to the TMA unit as a 2-D tensor and
+        // goes to the strided kernels (throughput or latency kernel by launch size), like device-resident input.
+        bool uniform = np >= 1 && !ragged && !job.init_states && !job.nonfinal && !job.prior && tma_loader >= 2;
+        uint64_t ustride = 0;
+        if (uniform) {
+            const uint64_t ulen = pieces[0].len;
+            ustride = np > 1 ? pieces[1].dst - pieces[0].dst : ((ulen + 15) & ~(uint64_t)15);
+            uniform = ulen >= 1 && ulen <= ctx->row_max && (pieces[0].dst & 15) == 0 && (ustride & 15) == 0 && ustride >= ulen &&
+                      tma_layout_ok(s.d_stage[bi] + pieces[0].dst, ustride, np);
+            for (size_t i = 0; i < np && uniform; ++i) {
+                const Piece &p = pieces[i];
+                uniform = p.src_off == 0 && p.last && p.len == ulen && p.unit == pieces[0].unit + i && p.dst == pieces[0].dst + i * ustride;
+            }
+        }
         // descriptor rows [i0, i1) of this batch; run on the pool next to the packing, or, in direct mode,
         // by this thread while the data copy is already under way
         auto fill_desc = [&](size_t i0, size_t i1) {
+            if (uniform) return;
             for (size_t i = i0; i < i1; ++i) {
                 const Piece &p = pieces[order[i]];
                 const uint32_t u = units[p.unit];
@@ -1110,12 +1160,14 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
                     if (r != 0) fail_io(r, u);
                 }
             };
+            const double tr_f0 = trace_now();
             ctx->pool->parallel_for(tasks.size(), 1, fill);
+            tr_fill += trace_now() - tr_f0;
             if (io_err.load() != 0) break;
             if (used) CU(cudaMemcpyAsync(s.d_stage[bi], stage, used, cudaMemcpyHostToDevice, s.s_copy));
         }
         // descriptors: five arrays, copied as stored (their device mirror has the same carving)
-        if (np) CU(cudaMemcpyAsync(s.d_desc_raw[bi], s.h_desc_raw[bi], np * desc_bytes_per_lane, cudaMemcpyHostToDevice, s.s_copy));
+        if (np && !uniform) CU(cudaMemcpyAsync(s.d_desc_raw[bi], s.h_desc_raw[bi], np * desc_bytes_per_lane, cudaMemcpyHostToDevice, s.s_copy));
         CU(cudaEventRecord(s.ev_copied[bi], s.s_copy));
 
         // ---- hash ------------------------------------------------------------------------------
@@ -1128,7 +1180,9 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
         a.off = dv.off; a.len = dv.len; a.prior = dv.prior;
         a.flags = dv.flags; a.out_idx = dv.oidx;
         a.table = s.d_table; a.n = np;
-        rc = launch_lanes(ctx, a, aligned, sk);
+        if (uniform) rc = launch_strided_tma(ctx, s.d_stage[bi] + pieces[0].dst, ustride, pieces[0].len, np, s.d_table + pieces[0].unit,
+                                             tma_loader, tma_shape, tma_mode, sk);
+        else rc = launch_lanes(ctx, a, aligned, sk);
         if (rc) return rc;
         CU(cudaEventRecord(s.ev_done[bi], sk));
         ++batch;
@@ -1148,7 +1202,11 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
     // ---- digests home -------------------------------------------------------------------------
     for (int b = 0; b < NBUF && b < batch; ++b) CU(cudaStreamWaitEvent(s.s_copy, s.ev_done[b], 0));
     CU(cudaMemcpyAsync(s.h_table, s.d_table, nu * 16, cudaMemcpyDeviceToHost, s.s_copy));
+    const double tr_s0 = trace_now();
     CU(cudaStreamSynchronize(s.s_copy));
+    if (trace_on())
+        fprintf(stderr, "[tpimd5] device %d: %zu units, %d batches, total %.1f ms: plan %.1f, buffer wait %.1f, fill %.1f, final sync %.1f\n",
+                s.dev, nu, batch, 1e3 * (trace_now() - tr0), 1e3 * tr_plan, 1e3 * tr_wait, 1e3 * tr_fill, 1e3 * (trace_now() - tr_s0));
     // table row i belongs to unit units[i]; runs of consecutive units move as one copy
     for (size_t i = 0; i < nu;) {
         size_t j = i + 1;

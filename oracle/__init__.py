@@ -142,8 +142,11 @@ def md5_batch(base, offsets, lengths, threads: int = 1, engine: int = ENGINE_RES
 
 def md5_files(paths, threads: int = 1, engine: int = ENGINE_RESTATED) -> np.ndarray:
     """rclone-shaped file hashing: one file per worker, 32 KiB reads -> uint8[n,16]."""
-    n = len(paths)
-    arr = (C.c_char_p * max(1, n))(*[os.fsencode(p) for p in paths])
+    if hasattr(paths, "array") and hasattr(paths, "n"):      # a pre-encoded listing (same shape as the binding's PathList)
+        n, arr = paths.n, paths.array
+    else:
+        n = len(paths)
+        arr = (C.c_char_p * max(1, n))(*[os.fsencode(p) for p in paths])
     out = np.zeros((n, 16), dtype=np.uint8)
     if lib().orc_md5_files(engine, C.cast(arr, C.c_void_p), n, out.ctypes.data, threads) != 0:
         raise OSError("orc_md5_files: a file could not be read")

@@ -14,6 +14,7 @@ at the repo root.
 """
 from .binding import (  # noqa: F401
     Context,
+    PathList,
     Stream,
     TpiMd5Error,
     NOALLOC_MAX_PARTS,
@@ -36,6 +37,6 @@ from .manifest import Filter, Manifest, plan_transfer  # noqa: F401,E402
 
 __all__ = [
     "Filter", "Manifest", "plan_transfer", "machine", "manifest", "sharding",
-    "Context", "Stream", "TpiMd5Error", "NOALLOC_MAX_PARTS", "dev_s3_etag_noalloc", "device_count", "lib_path", "load_library",
+    "Context", "PathList", "Stream", "TpiMd5Error", "NOALLOC_MAX_PARTS", "dev_s3_etag_noalloc", "device_count", "lib_path", "load_library",
     "s3_etag_text", "s3_nparts", "s3_part_size", "s3_plan_parts", "shard_lpt",
 ]

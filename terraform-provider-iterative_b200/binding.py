@@ -211,6 +211,19 @@ def _ptr(x) -> Optional[int]:
     return int(x)
 
 
+class PathList:
+    """A listing's paths as the C array the file entry points take (char *const *), built once and reused: a caller
+    that hashes the same listing again (a checkpoint loop) does not pay for re-encoding 10^5..10^6 strings."""
+
+    def __init__(self, paths: Sequence[str]):
+        self.n = len(paths)
+        self._keep = [os.fsencode(p) for p in paths]
+        self.array = (C.c_char_p * max(1, self.n))(*self._keep)
+
+    def __len__(self) -> int:
+        return self.n
+
+
 class Context:
     """One library context = a set of B200s plus their staging memory (tpimd5_init/destroy)."""
 
@@ -263,9 +276,10 @@ class Context:
         _check(self._L.tpimd5_hash_buffers(self._h, bp, off.ctypes.data, ln.ctypes.data, off.size, out.ctypes.data))
         return out
 
-    def hash_files(self, paths: Sequence[str], sizes=None) -> np.ndarray:
-        n = len(paths)
-        arr = (C.c_char_p * n)(*[os.fsencode(p) for p in paths])
+    def hash_files(self, paths, sizes=None) -> np.ndarray:
+        """paths: a sequence of str, or a PathList built once for a listing that is hashed repeatedly."""
+        pl = paths if isinstance(paths, PathList) else PathList(paths)
+        n, arr = pl.n, pl.array
         sz = None if sizes is None else np.ascontiguousarray(sizes, dtype=np.uint64)
         out = np.zeros((n, 16), dtype=np.uint8)
         failed = C.c_size_t()
