@@ -19,6 +19,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <deque>
 #include <fcntl.h>
 #include <functional>
 #include <memory>
@@ -108,7 +109,9 @@ class Pool {
         for (auto &t : th_) t.join();
     }
     int size() const { return (int)th_.size(); }
-    // fn(i) for i in [0, n), dynamically chunked; returns when all are done.  Callers may overlap.
+    // fn(i) for i in [0, n), dynamically chunked; returns when all are done.  Callers may overlap: each call
+    // waits for its own ITEMS only (not for the helpers it asked for -- those may still be busy with another
+    // caller's work and find nothing left when they get here), and requests are served first come, first served.
     void parallel_for(size_t n, size_t grain, const std::function<void(size_t)> &fn) {
         if (n == 0) return;
         if (th_.empty() || n <= grain) {
@@ -118,7 +121,6 @@ class Pool {
         auto job = std::make_shared<Job>();
         job->n = n; job->grain = grain; job->fn = &fn;
         size_t helpers = std::min<size_t>(th_.size(), (n + grain - 1) / grain);
-        job->pending = helpers + 1;
         {
             std::lock_guard<std::mutex> g(mu_);
             for (size_t i = 0; i < helpers; ++i) q_.push_back(job);
@@ -126,17 +128,17 @@ class Pool {
         cv_.notify_all();
         work(*job);                      // the caller helps too
         std::unique_lock<std::mutex> lk(job->mu);
-        job->cv.wait(lk, [&] { return job->pending == 0; });
+        job->cv.wait(lk, [&] { return job->done == job->n; });
     }
 
   private:
     struct Job {
         size_t n = 0, grain = 1;
         std::atomic<size_t> next{0};
-        const std::function<void(size_t)> *fn = nullptr;
+        const std::function<void(size_t)> *fn = nullptr;   // the caller's; only dereferenced for an item < n, i.e. before the caller returns
         std::mutex mu;
         std::condition_variable cv;
-        size_t pending = 0;
+        size_t done = 0;                 // items finished
     };
     static void work(Job &j) {
         for (;;) {
@@ -144,9 +146,10 @@ class Pool {
             if (lo >= j.n) break;
             size_t hi = std::min(j.n, lo + j.grain);
             for (size_t i = lo; i < hi; ++i) (*j.fn)(i);
+            std::lock_guard<std::mutex> g(j.mu);
+            j.done += hi - lo;
+            if (j.done == j.n) j.cv.notify_all();
         }
-        std::lock_guard<std::mutex> g(j.mu);
-        if (--j.pending == 0) j.cv.notify_all();
     }
     // Reader threads get a file-descriptor table of their own.  open() and close() serialise on a lock of the
     // table, which all threads of a process normally share: 16 threads reading 4 KiB files reach 1.5 M files/s
@@ -169,14 +172,14 @@ class Pool {
                 std::unique_lock<std::mutex> lk(mu_);
                 cv_.wait(lk, [&] { return stop_ || !q_.empty(); });
                 if (stop_ && q_.empty()) return;
-                job = q_.back();
-                q_.pop_back();
+                job = q_.front();
+                q_.pop_front();
             }
             work(*job);
         }
     }
     std::vector<std::thread> th_;
-    std::vector<std::shared_ptr<Job>> q_;
+    std::deque<std::shared_ptr<Job>> q_;
     std::mutex mu_;
     std::condition_variable cv_;
     bool stop_ = false;
@@ -196,26 +199,132 @@ struct LaneDesc {  // device / pinned mirrors, structure of arrays
     uint32_t *flags = nullptr, *oidx = nullptr;
 };
 
+// A digest / chaining-value table of one call: device rows and their pinned host mirror.
+struct TableBuf {
+    uint4 *d = nullptr;
+    uint8_t *h = nullptr;
+    size_t cap = 0;   // rows
+};
+// A plain block of device memory of one call (the host-pointer diff's inputs and outputs).
+struct DevBlock {
+    uint8_t *d = nullptr;
+    size_t cap = 0;   // bytes
+};
+
+// Host threads that belong to one device of a multi-device context: they run that device's share of a call
+// (planning, staging, launches), so that a call does not start and join a thread per device.  Two per
+// device, so two calls can be in flight on a device at once; bound to the CPUs the kernel lists as local to
+// the GPU (/sys/bus/pci/devices/<id>/local_cpulist), where that is a proper subset of the allowed CPUs.
+class DevWorkers {
+  public:
+    DevWorkers(int dev, int n) {
+        std::vector<int> cpus = local_cpus(dev);
+        for (int i = 0; i < n; ++i)
+            th_.emplace_back([this, cpus] {
+                if (!cpus.empty()) {
+                    cpu_set_t set;
+                    CPU_ZERO(&set);
+                    for (int c : cpus) CPU_SET(c, &set);
+                    sched_setaffinity(0, sizeof set, &set);
+                }
+                run();
+            });
+    }
+    ~DevWorkers() {
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            stop_ = true;
+        }
+        cv_.notify_all();
+        for (auto &t : th_) t.join();
+    }
+    void post(std::function<void()> fn) {
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            q_.push_back(std::move(fn));
+        }
+        cv_.notify_one();
+    }
+
+  private:
+    static std::vector<int> local_cpus(int dev) {
+        std::vector<int> out;
+        char id[32] = {0};
+        if (cudaDeviceGetPCIBusId(id, sizeof id, dev) != cudaSuccess) return out;
+        for (char *c = id; *c; ++c) *c = (char)tolower(*c);
+        const std::string path = std::string("/sys/bus/pci/devices/") + id + "/local_cpulist";
+        FILE *f = fopen(path.c_str(), "r");
+        if (!f) return out;
+        char line[4096] = {0};
+        const bool ok = fgets(line, sizeof line, f) != nullptr;
+        fclose(f);
+        if (!ok) return out;
+        cpu_set_t allowed;
+        CPU_ZERO(&allowed);
+        if (sched_getaffinity(0, sizeof allowed, &allowed) != 0) return out;
+        for (char *p = line; *p && *p != '\n';) {
+            char *end;
+            long a = strtol(p, &end, 10), b = a;
+            if (end == p) break;
+            if (*end == '-') { p = end + 1; b = strtol(p, &end, 10); }
+            for (long c = a; c <= b && c < CPU_SETSIZE; ++c)
+                if (CPU_ISSET((int)c, &allowed)) out.push_back((int)c);
+            p = *end == ',' ? end + 1 : end;
+        }
+        if ((int)out.size() >= CPU_COUNT(&allowed) || out.size() < 2) out.clear();   // not a proper subset: nothing to gain
+        return out;
+    }
+    void run() {
+        for (;;) {
+            std::function<void()> fn;
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                cv_.wait(lk, [&] { return stop_ || !q_.empty(); });
+                if (q_.empty()) return;
+                fn = std::move(q_.front());
+                q_.pop_front();
+            }
+            fn();
+        }
+    }
+    std::vector<std::thread> th_;
+    std::deque<std::function<void()>> q_;
+    std::mutex mu_;
+    std::condition_variable cv_;
+    bool stop_ = false;
+};
+
+// One device of a context.  Nothing here is held for the length of a call: callers LEASE what they need --
+// staging buffers one at a time out of the slot's NBUF, a table, a stream -- so that several calls (Terraform
+// runs ~10 resource operations in one plugin process, rclone calls from 12 goroutines) overlap on one GPU.
+// `mu` only guards the free lists.
 struct Slot {
     int dev = -1;
-    std::mutex mu;  // one call at a time per device
-    cudaStream_t s_copy = nullptr, s_comp = nullptr;
-    cudaStream_t s_batch[NBUF] = {};  // one per staging buffer: kernels of successive batches overlap, which is
-                                      // what keeps many chains in flight when single units take tens of ms
+    std::mutex mu;
+    std::condition_variable cv;          // a staging buffer came back
+    cudaStream_t s_comp = nullptr;
+    cudaStream_t s_batch[NBUF] = {};     // one per staging buffer (copy, then kernel): successive batches overlap, which
+                                         // is what keeps many chains in flight when single units take tens of ms
     // ingest staging (allocated on first use)
     size_t stage_bytes = 0;
     uint8_t *h_stage[NBUF] = {}, *d_stage[NBUF] = {};
     uint8_t *h_desc_raw[NBUF] = {}, *d_desc_raw[NBUF] = {};
-    cudaEvent_t ev_copied[NBUF] = {}, ev_done[NBUF] = {};
-    // digest / chaining-value table
-    uint4 *d_table = nullptr;
-    uint8_t *h_table = nullptr;
-    size_t table_cap = 0;
-    // scratch: S3 part digests, diff tile counts
+    cudaEvent_t ev_done[NBUF] = {};
+    bool buf_free[NBUF];
+    int n_free = NBUF;
+    int active_calls = 0;                // host calls that hold a lease on this slot right now
+    // free lists, kept until tpimd5_destroy
+    std::vector<TableBuf> free_tables;
+    std::vector<DevBlock> free_blocks;
+    std::vector<cudaStream_t> free_streams;
+    // scratch of the tpimd5_dev_* calls: S3 part digests, diff tile counts, bucketing temporaries
+    std::mutex scratch_mu;
     uint8_t *d_scratch = nullptr;
     size_t scratch_cap = 0;
     std::vector<uint8_t *> retired;   // outgrown scratch buffers: a call that captured the old pointer may still be
                                       // launching on it, so they are only freed in tpimd5_destroy
+    std::unique_ptr<DevWorkers> workers;  // contexts over several devices: this device's host threads
+    Slot() { for (bool &b : buf_free) b = true; }
 };
 
 struct tpimd5_ctx {
@@ -239,17 +348,93 @@ static void carve_desc(uint8_t *raw, size_t cap, LaneDesc &d) {
     d.oidx = d.flags + cap;
 }
 
-static int ensure_table(Slot &s, size_t rows) {
-    if (rows <= s.table_cap) return 0;
-    size_t cap = std::max<size_t>(rows, 4096);
-    cap = (cap + 4095) & ~(size_t)4095;
-    if (s.d_table) cudaFree(s.d_table);
-    if (s.h_table) cudaFreeHost(s.h_table);
-    s.d_table = nullptr; s.h_table = nullptr; s.table_cap = 0;
-    CU(cudaMalloc(&s.d_table, cap * 16));
-    CU(cudaHostAlloc(&s.h_table, cap * 16, cudaHostAllocDefault));
-    s.table_cap = cap;
+// ---- leases ----------------------------------------------------------------------------------------
+static int take_table(Slot &s, size_t rows, TableBuf &out) {
+    {
+        std::lock_guard<std::mutex> g(s.mu);
+        int best = -1;
+        for (int i = 0; i < (int)s.free_tables.size(); ++i)
+            if (s.free_tables[i].cap >= rows && (best < 0 || s.free_tables[i].cap < s.free_tables[best].cap)) best = i;
+        if (best >= 0) {
+            out = s.free_tables[best];
+            s.free_tables.erase(s.free_tables.begin() + best);
+            return 0;
+        }
+        if (!s.free_tables.empty()) {            // all too small: let the largest of them go instead of piling up
+            int big = 0;
+            for (int i = 1; i < (int)s.free_tables.size(); ++i)
+                if (s.free_tables[i].cap > s.free_tables[big].cap) big = i;
+            out = s.free_tables[big];
+            s.free_tables.erase(s.free_tables.begin() + big);
+        }
+    }
+    if (out.d) cudaFree(out.d);
+    if (out.h) cudaFreeHost(out.h);
+    out = TableBuf{};
+    size_t cap = (std::max<size_t>(rows, 4096) + 4095) & ~(size_t)4095;
+    CU(cudaMalloc(&out.d, cap * 16));
+    if (cudaHostAlloc(&out.h, cap * 16, cudaHostAllocDefault) != cudaSuccess) {
+        cudaFree(out.d);
+        out = TableBuf{};
+        return fail(TPIMD5_ENOMEM, "pinned host memory for %zu digests", cap);
+    }
+    out.cap = cap;
     return 0;
+}
+static void give_table(Slot &s, TableBuf &t) {
+    if (!t.d) return;
+    std::lock_guard<std::mutex> g(s.mu);
+    s.free_tables.push_back(t);
+    t = TableBuf{};
+}
+
+static int take_block(Slot &s, size_t bytes, DevBlock &out) {
+    {
+        std::lock_guard<std::mutex> g(s.mu);
+        int best = -1;
+        for (int i = 0; i < (int)s.free_blocks.size(); ++i)
+            if (s.free_blocks[i].cap >= bytes && (best < 0 || s.free_blocks[i].cap < s.free_blocks[best].cap)) best = i;
+        if (best >= 0) {
+            out = s.free_blocks[best];
+            s.free_blocks.erase(s.free_blocks.begin() + best);
+            return 0;
+        }
+        if (!s.free_blocks.empty()) {
+            out = s.free_blocks.back();
+            s.free_blocks.pop_back();
+        }
+    }
+    if (out.d) cudaFree(out.d);
+    out = DevBlock{};
+    const size_t cap = (std::max<size_t>(bytes, 1u << 20) + 255) & ~(size_t)255;
+    CU(cudaMalloc(&out.d, cap));
+    out.cap = cap;
+    return 0;
+}
+static void give_block(Slot &s, DevBlock &b) {
+    if (!b.d) return;
+    std::lock_guard<std::mutex> g(s.mu);
+    s.free_blocks.push_back(b);
+    b = DevBlock{};
+}
+
+static int take_stream(Slot &s, cudaStream_t &out) {
+    {
+        std::lock_guard<std::mutex> g(s.mu);
+        if (!s.free_streams.empty()) {
+            out = s.free_streams.back();
+            s.free_streams.pop_back();
+            return 0;
+        }
+    }
+    CU(cudaStreamCreateWithFlags(&out, cudaStreamNonBlocking));
+    return 0;
+}
+static void give_stream(Slot &s, cudaStream_t &st) {
+    if (!st) return;
+    std::lock_guard<std::mutex> g(s.mu);
+    s.free_streams.push_back(st);
+    st = nullptr;
 }
 
 static int ensure_scratch(Slot &s, size_t bytes) {
@@ -272,7 +457,6 @@ static int ensure_buffer(tpimd5_ctx *ctx, Slot &s, int i, bool need_host) {
         CU(cudaMalloc(&s.d_stage[i], s.stage_bytes + 256));
         CU(cudaHostAlloc(&s.h_desc_raw[i], MAX_BATCH_LANES * desc_bytes_per_lane, cudaHostAllocDefault));
         CU(cudaMalloc(&s.d_desc_raw[i], MAX_BATCH_LANES * desc_bytes_per_lane));
-        CU(cudaEventCreateWithFlags(&s.ev_copied[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&s.ev_done[i], cudaEventDisableTiming));
     }
     if (need_host && !s.h_stage[i]) CU(cudaHostAlloc(&s.h_stage[i], s.stage_bytes + 256, cudaHostAllocDefault));
@@ -308,8 +492,8 @@ extern "C" int tpimd5_init(const int *device_ids, int n_devices, size_t staging_
                         prop.major, prop.minor);
         std::unique_ptr<Slot> s(new Slot);
         s->dev = dev;
+        s->stage_bytes = ctx->staging;
         USE_DEVICE(dev);
-        CU(cudaStreamCreateWithFlags(&s->s_copy, cudaStreamNonBlocking));
         CU(cudaStreamCreateWithFlags(&s->s_comp, cudaStreamNonBlocking));
         for (int b = 0; b < NBUF; ++b) CU(cudaStreamCreateWithFlags(&s->s_batch[b], cudaStreamNonBlocking));
         ctx->slots.push_back(std::move(s));
@@ -322,6 +506,8 @@ extern "C" int tpimd5_init(const int *device_ids, int n_devices, size_t staging_
         const uint64_t v = strtoull(e, nullptr, 0);
         if (v >= 64 && v <= ((uint64_t)1 << 30) && v % 64 == 0) ctx->chain_seg = v;
     }
+    if (ctx->slots.size() > 1)
+        for (auto &sp : ctx->slots) sp->workers.reset(new DevWorkers(sp->dev, 2));
     unsigned hc = std::thread::hardware_concurrency();
     int workers = (int)std::min<unsigned>(hc ? hc : 4, 32);
     ctx->pool.reset(new Pool(workers > 1 ? workers - 1 : 0));
@@ -331,26 +517,25 @@ extern "C" int tpimd5_init(const int *device_ids, int n_devices, size_t staging_
 
 extern "C" void tpimd5_destroy(tpimd5_ctx *ctx) {
     if (!ctx) return;
+    for (auto &sp : ctx->slots) sp->workers.reset();
     for (auto &sp : ctx->slots) {
         Slot &s = *sp;
         DeviceGuard guard(s.dev);
         if (s.s_comp) cudaStreamSynchronize(s.s_comp);
         for (int b = 0; b < NBUF; ++b)
             if (s.s_batch[b]) { cudaStreamSynchronize(s.s_batch[b]); cudaStreamDestroy(s.s_batch[b]); }
-        if (s.s_copy) cudaStreamSynchronize(s.s_copy);
         for (int i = 0; i < NBUF; ++i) {
             if (s.h_stage[i]) cudaFreeHost(s.h_stage[i]);
             if (s.d_stage[i]) cudaFree(s.d_stage[i]);
             if (s.h_desc_raw[i]) cudaFreeHost(s.h_desc_raw[i]);
             if (s.d_desc_raw[i]) cudaFree(s.d_desc_raw[i]);
-            if (s.ev_copied[i]) cudaEventDestroy(s.ev_copied[i]);
             if (s.ev_done[i]) cudaEventDestroy(s.ev_done[i]);
         }
-        if (s.d_table) cudaFree(s.d_table);
-        if (s.h_table) cudaFreeHost(s.h_table);
+        for (TableBuf &t : s.free_tables) { cudaFree(t.d); cudaFreeHost(t.h); }
+        for (DevBlock &b : s.free_blocks) cudaFree(b.d);
+        for (cudaStream_t st : s.free_streams) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
         if (s.d_scratch) cudaFree(s.d_scratch);
         for (uint8_t *p : s.retired) cudaFree(p);
-        if (s.s_copy) cudaStreamDestroy(s.s_copy);
         if (s.s_comp) cudaStreamDestroy(s.s_comp);
     }
     delete ctx;
@@ -709,7 +894,7 @@ extern "C" int tpimd5_dev_hash_buffers(tpimd5_ctx *ctx, int slot, const void *d_
     const size_t n4 = (n * 4 + 255) & ~(size_t)255, n8 = (n * 8 + 255) & ~(size_t)255;
     uint8_t *base_scratch;
     {
-        std::lock_guard<std::mutex> g(s->mu);      // the scratch is shared by calls on this slot
+        std::lock_guard<std::mutex> g(s->scratch_mu);      // the scratch is shared by calls on this slot
         int rc = ensure_scratch(*s, 4 * n4 + 2 * n8 + cub_bytes + 256);
         if (rc) return rc;
         base_scratch = s->d_scratch;
@@ -756,7 +941,7 @@ extern "C" int tpimd5_dev_s3_etag(tpimd5_ctx *ctx, int slot, const void *d_data,
     uint8_t *parts = (uint8_t *)d_part_digests;
     if (!parts) {
         // library scratch: shared by the slot, so serialise callers that rely on it
-        std::lock_guard<std::mutex> g(s->mu);
+        std::lock_guard<std::mutex> g(s->scratch_mu);
         int rc = ensure_scratch(*s, (size_t)np * 16);
         if (rc) return rc;
         parts = s->d_scratch;
@@ -799,7 +984,7 @@ extern "C" int tpimd5_dev_diff(tpimd5_ctx *ctx, int slot, const void *d_old16, c
     uint64_t *counts;
     {
         // tile counts live in the slot's scratch, which calls on this slot share
-        std::lock_guard<std::mutex> g(s->mu);
+        std::lock_guard<std::mutex> g(s->scratch_mu);
         int rc = ensure_scratch(*s, ((n + DIFF_TILE - 1) / DIFF_TILE) * sizeof(uint64_t));
         if (rc) return rc;
         counts = (uint64_t *)s->d_scratch;
@@ -931,6 +1116,93 @@ static int read_fully(int fd, uint8_t *dst, uint64_t off, uint64_t n, bool probe
     return 0;
 }
 
+// What one host call holds on one device while it runs: a table, a stream of its own, and the staging
+// buffers it has drawn so far (oldest first).  Giving everything back is the destructor's job, after every
+// stream the call used has drained -- whatever went wrong, no copy out of caller memory and no kernel is
+// left in flight when the call returns, so the caller may free its buffers right away.
+struct Lease {
+    Slot &s;
+    TableBuf table;
+    cudaStream_t stream = nullptr;
+    std::vector<int> bufs;      // staging buffers held, in the order they will be reused
+    size_t next = 0;            // index in bufs of the oldest batch in flight
+    bool counted = false;
+    explicit Lease(Slot &slot) : s(slot) {}
+    Lease(const Lease &) = delete;
+    Lease &operator=(const Lease &) = delete;
+    int begin(size_t rows) {
+        {
+            std::lock_guard<std::mutex> g(s.mu);
+            ++s.active_calls;
+            counted = true;
+        }
+        int rc = take_table(s, rows, table);
+        if (rc) return rc;
+        return take_stream(s, stream);
+    }
+    // A staging buffer for the next batch.  While the call is alone on the device it may draw all NBUF; with
+    // other calls in flight it stays within its share (NBUF / calls, at least one) and hands its surplus
+    // back as those batches drain.  At its limit the call recycles its own oldest buffer (waiting for that
+    // batch's kernel); a call that holds none waits for one to come back -- a call that holds some never
+    // does, so calls cannot block each other.
+    int acquire(int &bi_out) {
+        for (;;) {
+            bool shed = false;
+            {
+                std::unique_lock<std::mutex> lk(s.mu);
+                for (;;) {
+                    const int share = std::max(1, NBUF / std::max(1, s.active_calls));
+                    if ((int)bufs.size() < share && s.n_free > 0) {
+                        for (int i = 0; i < NBUF; ++i)
+                            if (s.buf_free[i]) {
+                                s.buf_free[i] = false;
+                                --s.n_free;
+                                bufs.insert(bufs.begin() + next, i);   // in front of the oldest: it is the newest now
+                                ++next;
+                                if (next >= bufs.size()) next = 0;
+                                bi_out = i;
+                                return 0;
+                            }
+                    }
+                    if (!bufs.empty()) {
+                        shed = (int)bufs.size() > share;    // others have arrived: hand the surplus back as it drains
+                        break;
+                    }
+                    s.cv.wait(lk);
+                }
+            }
+            const int bi = bufs[next];
+            CU(cudaEventSynchronize(s.ev_done[bi]));
+            if (!shed) {
+                next = (next + 1) % bufs.size();
+                bi_out = bi;
+                return 0;
+            }
+            bufs.erase(bufs.begin() + next);
+            if (next >= bufs.size()) next = 0;
+            {
+                std::lock_guard<std::mutex> g(s.mu);
+                s.buf_free[bi] = true;
+                ++s.n_free;
+            }
+            s.cv.notify_all();
+        }
+    }
+    ~Lease() {
+        for (int bi : bufs)
+            if (s.s_batch[bi]) cudaStreamSynchronize(s.s_batch[bi]);
+        if (stream) cudaStreamSynchronize(stream);
+        give_table(s, table);
+        give_stream(s, stream);
+        {
+            std::lock_guard<std::mutex> g(s.mu);
+            for (int bi : bufs) { s.buf_free[bi] = true; ++s.n_free; }
+            if (counted) --s.active_calls;
+        }
+        s.cv.notify_all();
+    }
+};
+
 // TPIMD5_TRACE=1: phase timings of the ingest pipeline on stderr (diagnostics only)
 static bool trace_on() {
     static const bool on = [] { const char *e = getenv("TPIMD5_TRACE"); return e && e[0] == '1'; }();
@@ -954,16 +1226,19 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
     }
     const std::vector<uint32_t> &units = job.paths ? by_size : units_in;
     USE_DEVICE(s.dev);
-    s.stage_bytes = ctx->staging;
-    int rc = ensure_table(s, units.size());
+    Lease lease(s);                       // declared after the device guard: it drains its streams before the device is put back
+    int rc = lease.begin(units.size());
     if (rc) return rc;
+    uint4 *const d_table = lease.table.d;
+    uint8_t *const h_table = lease.table.h;
     const size_t nu = units.size();
     const bool from_files = job.paths != nullptr;
 
     // chaining values to start from
     if (job.init_states) {
-        for (size_t i = 0; i < nu; ++i) memcpy(s.h_table + 16 * i, job.init_states + 16 * (size_t)units[i], 16);
-        CU(cudaMemcpyAsync(s.d_table, s.h_table, nu * 16, cudaMemcpyHostToDevice, s.s_copy));   // before any batch's data
+        for (size_t i = 0; i < nu; ++i) memcpy(h_table + 16 * i, job.init_states + 16 * (size_t)units[i], 16);
+        CU(cudaMemcpyAsync(d_table, h_table, nu * 16, cudaMemcpyHostToDevice, lease.stream));
+        CU(cudaStreamSynchronize(lease.stream));    // in place before any batch's kernel reads it (a few KiB)
     }
 
     // Direct mode: units already lie close together and in order in caller memory, so each batch is
@@ -999,12 +1274,17 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
     std::vector<uint32_t> order;
     size_t ui = 0;            // next unit
     uint64_t consumed = 0;    // bytes of units[ui] already planned
-    int batch = 0;
+    int batch = 0, prev_bi = -1;
     std::atomic<int> io_err{0};
     std::atomic<size_t> io_idx{(size_t)-1};
 
     while (ui < nu) {
-        const int bi = batch % NBUF;
+        // ---- a staging buffer: a fresh one, or this call's oldest once its batch has been consumed ----
+        const double tr_w0 = trace_now();
+        int bi = -1;
+        rc = lease.acquire(bi);
+        if (rc) return rc;
+        tr_wait += trace_now() - tr_w0;
         rc = ensure_buffer(ctx, s, bi, !direct);
         if (rc) return rc;
         const double tr_b0 = trace_now();
@@ -1044,11 +1324,7 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
         }
         const size_t np = pieces.size();
 
-        // ---- wait until this staging buffer's previous batch has been consumed -----------------
-        const double tr_b1 = trace_now();
-        if (batch >= NBUF) CU(cudaEventSynchronize(s.ev_done[bi]));
-        tr_plan += tr_b1 - tr_b0;
-        tr_wait += trace_now() - tr_b1;
+        tr_plan += trace_now() - tr_b0;
 
         // ---- lanes, longest first so that a warp's 32 units finish together ---------------------
         order.resize(np);
@@ -1099,7 +1375,7 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
 
         // ---- bring the bytes to the device -----------------------------------------------------
         if (direct) {
-            if (used > shift) CU(cudaMemcpyAsync(s.d_stage[bi] + shift, job.base + lo, used - shift, cudaMemcpyHostToDevice, s.s_copy));
+            if (used > shift) CU(cudaMemcpyAsync(s.d_stage[bi] + shift, job.base + lo, used - shift, cudaMemcpyHostToDevice, s.s_batch[bi]));
             fill_desc(0, np);
         } else {
             uint8_t *stage = s.h_stage[bi];
@@ -1164,33 +1440,30 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
             ctx->pool->parallel_for(tasks.size(), 1, fill);
             tr_fill += trace_now() - tr_f0;
             if (io_err.load() != 0) break;
-            if (used) CU(cudaMemcpyAsync(s.d_stage[bi], stage, used, cudaMemcpyHostToDevice, s.s_copy));
+            if (used) CU(cudaMemcpyAsync(s.d_stage[bi], stage, used, cudaMemcpyHostToDevice, s.s_batch[bi]));
         }
         // descriptors: five arrays, copied as stored (their device mirror has the same carving)
-        if (np && !uniform) CU(cudaMemcpyAsync(s.d_desc_raw[bi], s.h_desc_raw[bi], np * desc_bytes_per_lane, cudaMemcpyHostToDevice, s.s_copy));
-        CU(cudaEventRecord(s.ev_copied[bi], s.s_copy));
+        if (np && !uniform) CU(cudaMemcpyAsync(s.d_desc_raw[bi], s.h_desc_raw[bi], np * desc_bytes_per_lane, cudaMemcpyHostToDevice, s.s_batch[bi]));
 
-        // ---- hash ------------------------------------------------------------------------------
+        // ---- hash (same stream: the kernel follows its batch's copies) -----------------------------
         cudaStream_t sk = s.s_batch[bi];
-        CU(cudaStreamWaitEvent(sk, s.ev_copied[bi], 0));
         // a unit continued from the previous batch reads the chaining value that batch's kernel writes
-        if (batch > 0 && np && pieces[0].src_off > 0) CU(cudaStreamWaitEvent(sk, s.ev_done[(batch - 1) % NBUF], 0));
+        if (batch > 0 && np && pieces[0].src_off > 0) CU(cudaStreamWaitEvent(sk, s.ev_done[prev_bi], 0));
         LaneArgs a{};
         a.base = s.d_stage[bi]; a.base_bytes = used;
         a.off = dv.off; a.len = dv.len; a.prior = dv.prior;
         a.flags = dv.flags; a.out_idx = dv.oidx;
-        a.table = s.d_table; a.n = np;
-        if (uniform) rc = launch_strided_tma(ctx, s.d_stage[bi] + pieces[0].dst, ustride, pieces[0].len, np, s.d_table + pieces[0].unit,
+        a.table = d_table; a.n = np;
+        if (uniform) rc = launch_strided_tma(ctx, s.d_stage[bi] + pieces[0].dst, ustride, pieces[0].len, np, d_table + pieces[0].unit,
                                              tma_loader, tma_shape, tma_mode, sk);
         else rc = launch_lanes(ctx, a, aligned, sk);
         if (rc) return rc;
         CU(cudaEventRecord(s.ev_done[bi], sk));
+        prev_bi = bi;
         ++batch;
     }
 
     if (io_err.load() != 0) {
-        cudaStreamSynchronize(s.s_copy);
-        for (int b = 0; b < NBUF; ++b) cudaStreamSynchronize(s.s_batch[b]);
         const size_t u = io_idx.load();
         job.failed_index = u;
         const int e = io_err.load();
@@ -1200,10 +1473,10 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
     }
 
     // ---- digests home -------------------------------------------------------------------------
-    for (int b = 0; b < NBUF && b < batch; ++b) CU(cudaStreamWaitEvent(s.s_copy, s.ev_done[b], 0));
-    CU(cudaMemcpyAsync(s.h_table, s.d_table, nu * 16, cudaMemcpyDeviceToHost, s.s_copy));
+    for (int b : lease.bufs) CU(cudaStreamWaitEvent(lease.stream, s.ev_done[b], 0));
+    CU(cudaMemcpyAsync(h_table, d_table, nu * 16, cudaMemcpyDeviceToHost, lease.stream));
     const double tr_s0 = trace_now();
-    CU(cudaStreamSynchronize(s.s_copy));
+    CU(cudaStreamSynchronize(lease.stream));
     if (trace_on())
         fprintf(stderr, "[tpimd5] device %d: %zu units, %d batches, total %.1f ms: plan %.1f, buffer wait %.1f, fill %.1f, final sync %.1f\n",
                 s.dev, nu, batch, 1e3 * (trace_now() - tr0), 1e3 * tr_plan, 1e3 * tr_wait, 1e3 * tr_fill, 1e3 * (trace_now() - tr_s0));
@@ -1211,26 +1484,15 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
     for (size_t i = 0; i < nu;) {
         size_t j = i + 1;
         while (j < nu && units[j] == units[j - 1] + 1) ++j;
-        memcpy(job.out + 16 * (size_t)units[i], s.h_table + 16 * i, 16 * (j - i));
+        memcpy(job.out + 16 * (size_t)units[i], h_table + 16 * i, 16 * (j - i));
         i = j;
     }
     return 0;
 }
 
-// Runs one device's share under the slot's lock.  Whatever goes wrong, no copy out of caller memory and
-// no kernel is left in flight when this returns: the caller may free its buffers right away.
+// Runs one device's share.  (The lease inside run_device_impl drains and returns everything on every path.)
 static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint32_t> &units) {
-    std::lock_guard<std::mutex> guard(s.mu);
-    const int rc = run_device_impl(ctx, s, job, units);
-    if (rc != 0) {
-        const std::string keep = g_err;                 // the first error is the one to report
-        DeviceGuard guard(s.dev);
-        cudaStreamSynchronize(s.s_copy);
-        for (int b = 0; b < NBUF; ++b)
-            if (s.s_batch[b]) cudaStreamSynchronize(s.s_batch[b]);
-        g_err = keep;
-    }
-    return rc;
+    return run_device_impl(ctx, s, job, units);
 }
 
 static int run_job(tpimd5_ctx *ctx, Job &job) {
@@ -1265,13 +1527,20 @@ static int run_job(tpimd5_ctx *ctx, Job &job) {
     }
     std::vector<int> rcs(ndev, 0);
     std::vector<std::string> errs(ndev);
-    std::vector<std::thread> th;
+    std::mutex done_mu;
+    std::condition_variable done_cv;
+    int pending = ndev;
     for (int d = 0; d < ndev; ++d)
-        th.emplace_back([&, d] {
-            rcs[d] = run_device(ctx, *ctx->slots[d], job, shards[d]);
+        ctx->slots[d]->workers->post([&, d] {
+            rcs[d] = shards[d].empty() ? 0 : run_device(ctx, *ctx->slots[d], job, shards[d]);
             if (rcs[d]) errs[d] = g_err;
+            std::lock_guard<std::mutex> g(done_mu);
+            if (--pending == 0) done_cv.notify_all();
         });
-    for (auto &t : th) t.join();
+    {
+        std::unique_lock<std::mutex> lk(done_mu);
+        done_cv.wait(lk, [&] { return pending == 0; });
+    }
     for (int d = 0; d < ndev; ++d)
         if (rcs[d]) {
             g_err = errs[d];
@@ -1463,41 +1732,38 @@ extern "C" int tpimd5_diff(tpimd5_ctx *ctx, const uint8_t *old16, const uint8_t 
     if (!old16 || !new16 || !changed_idx_out) return fail(TPIMD5_EINVAL, "diff: null pointer");
     if (n > 0xffffffffull) return fail(TPIMD5_ERANGE, "diff: more than 2^32 units");
     Slot &s = *ctx->slots[0];
-    std::lock_guard<std::mutex> guard(s.mu);
     USE_DEVICE(s.dev);
-    const size_t tiles = (n + DIFF_TILE - 1) / DIFF_TILE;   // tile counts: this call's own, not the slot's dev_* scratch
-    uint8_t *d_old = nullptr, *d_new = nullptr;
-    uint32_t *d_idx = nullptr;
-    uint64_t *d_cnt = nullptr;
-    int rc = 0;
+    // One block of device memory out of the slot's free list and a stream of the call's own: no allocation
+    // in the steady state, and concurrent diffs (or a diff next to a running hash job) do not wait for each other.
+    const size_t tiles = (n + DIFF_TILE - 1) / DIFF_TILE;
+    const size_t b_old = 0, b_new = n * 16, b_idx = 2 * n * 16, b_cnt = (b_idx + n * 4 + 255) & ~(size_t)255;
+    struct Held {
+        Slot &s;
+        DevBlock blk;
+        cudaStream_t st = nullptr;
+        explicit Held(Slot &slot) : s(slot) {}
+        ~Held() {
+            if (st) cudaStreamSynchronize(st);
+            give_block(s, blk);
+            give_stream(s, st);
+        }
+    } held(s);
+    int rc = take_block(s, b_cnt + 8 + tiles * sizeof(uint64_t), held.blk);
+    if (rc == 0) rc = take_stream(s, held.st);
+    if (rc) return rc;
+    uint8_t *const base = held.blk.d;
+    uint64_t *const d_cnt = (uint64_t *)(base + b_cnt);
     uint64_t cnt = 0;
-    auto cleanup = [&] {
-        if (d_old) cudaFree(d_old);
-        if (d_new) cudaFree(d_new);
-        if (d_idx) cudaFree(d_idx);
-        if (d_cnt) cudaFree(d_cnt);
-    };
-#define CUX(call)                                                                                     \
-    do {                                                                                              \
-        cudaError_t e_ = (call);                                                                      \
-        if (e_ != cudaSuccess) {                                                                      \
-            cleanup();                                                                                \
-            return fail(TPIMD5_ECUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
-        }                                                                                             \
-    } while (0)
-    CUX(cudaMalloc(&d_old, n * 16));
-    CUX(cudaMalloc(&d_new, n * 16));
-    CUX(cudaMalloc(&d_idx, n * 4));
-    CUX(cudaMalloc(&d_cnt, 8 + tiles * sizeof(uint64_t)));
-    CUX(cudaMemcpyAsync(d_old, old16, n * 16, cudaMemcpyHostToDevice, s.s_comp));
-    CUX(cudaMemcpyAsync(d_new, new16, n * 16, cudaMemcpyHostToDevice, s.s_comp));
-    rc = diff_launch(ctx, d_old, d_new, n, d_idx, d_cnt, d_cnt + 1, s.s_comp);
-    if (rc) { cleanup(); return rc; }
-    CUX(cudaMemcpyAsync(&cnt, d_cnt, 8, cudaMemcpyDeviceToHost, s.s_comp));
-    CUX(cudaStreamSynchronize(s.s_comp));
-    if (cnt) CUX(cudaMemcpy(changed_idx_out, d_idx, cnt * 4, cudaMemcpyDeviceToHost));
-#undef CUX
-    cleanup();
+    CU(cudaMemcpyAsync(base + b_old, old16, n * 16, cudaMemcpyHostToDevice, held.st));
+    CU(cudaMemcpyAsync(base + b_new, new16, n * 16, cudaMemcpyHostToDevice, held.st));
+    rc = diff_launch(ctx, base + b_old, base + b_new, n, (uint32_t *)(base + b_idx), d_cnt, d_cnt + 1, held.st);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(&cnt, d_cnt, 8, cudaMemcpyDeviceToHost, held.st));
+    CU(cudaStreamSynchronize(held.st));
+    if (cnt) {
+        CU(cudaMemcpyAsync(changed_idx_out, base + b_idx, cnt * 4, cudaMemcpyDeviceToHost, held.st));
+        CU(cudaStreamSynchronize(held.st));
+    }
     *n_changed_out = (size_t)cnt;
     return 0;
 }

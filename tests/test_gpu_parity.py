@@ -405,6 +405,22 @@ def test_one_context_many_threads(ctx):
     assert not errs, errs
 
 
+def test_concurrent_callers_overlap_on_one_gpu():
+    """Eight threads, one context, one GPU, each hashing its own workdir whose longest file is 8 MiB (one job is
+    bound by that file's serial chain and leaves the GPU almost idle): the calls lease staging buffers, tables
+    and streams instead of queueing behind one lock, so all eight take at most twice as long as one -- and
+    every digest is the oracle's."""
+    import subprocess
+    import sys
+    import json
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "bench_concurrent.py"), "8"], capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    rec = json.loads(r.stdout.strip().splitlines()[-1])
+    assert rec["bit_exact"] and rec["ratio"] <= 2.0, rec
+
+
 @pytest.mark.skipif(tpi.device_count() < 2, reason="needs two GPUs in one process")
 def test_one_context_two_devices_shards_and_gathers():
     """In-process multi-GPU: units split byte-balanced over the context's devices, digests gathered
