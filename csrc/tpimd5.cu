@@ -333,6 +333,8 @@ struct tpimd5_ctx {
     size_t staging = DEFAULT_STAGING;
     std::atomic<uint64_t> launches{0};
     std::atomic<int> variant{0};
+    // what tpimd5_get_progress reports (monotonic since tpimd5_init)
+    std::atomic<uint64_t> calls_started{0}, calls_finished{0}, units_done{0}, bytes_staged{0}, bytes_done{0};
     // longest tensor-map row, and bytes of a longer unit hashed per launch (tests shrink both through the
     // environment to run the segment logic on small data)
     uint64_t row_max = (uint64_t)1 << 31, chain_seg = (uint64_t)1 << 30;
@@ -542,6 +544,15 @@ extern "C" void tpimd5_destroy(tpimd5_ctx *ctx) {
 }
 
 extern "C" int tpimd5_ctx_devices(const tpimd5_ctx *ctx) { return ctx ? (int)ctx->slots.size() : 0; }
+extern "C" int tpimd5_get_progress(const tpimd5_ctx *ctx, tpimd5_progress *out) {
+    if (!ctx || !out) return fail(TPIMD5_EINVAL, "get_progress: null pointer");
+    out->calls_started = ctx->calls_started.load();
+    out->calls_finished = ctx->calls_finished.load();
+    out->units_done = ctx->units_done.load();
+    out->bytes_staged = ctx->bytes_staged.load();
+    out->bytes_done = ctx->bytes_done.load();
+    return 0;
+}
 extern "C" uint64_t tpimd5_launch_count(const tpimd5_ctx *ctx) { return ctx ? ctx->launches.load() : 0; }
 extern "C" int tpimd5_set_variant(tpimd5_ctx *ctx, int variant) {
     if (!ctx || variant < 0 || variant > 499) return fail(TPIMD5_EINVAL, "tpimd5_set_variant: 100*loader(0 cp.async, 2 tensor map for strided units, 3 / 4 latency kernel for strided units, 2 / 4 blocks per iteration) + 10*mode(0,4,6) + shape");
@@ -1213,7 +1224,18 @@ static double trace_now() {
 }
 
 // Runs one device's share of a job.  `units` are indices into the job.
-static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint32_t> &units_in) {
+// Units of a job that one device takes: an explicit list of indices, or the range [base, base + n) of the
+// caller's order (the common case: no per-unit vector is built for a listing of millions of files).
+struct UnitList {
+    const uint32_t *idx = nullptr;
+    uint32_t base = 0;
+    size_t n = 0;
+    uint32_t operator[](size_t i) const { return idx ? idx[i] : base + (uint32_t)i; }
+    size_t size() const { return n; }
+    bool empty() const { return n == 0; }
+};
+
+static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &units_in) {
     if (units_in.empty()) return 0;
     const double tr0 = trace_now();
     double tr_plan = 0, tr_fill = 0, tr_wait = 0;
@@ -1221,10 +1243,11 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
     // bounded by its longest file; starting those in the first batch lets the short ones fill in behind.
     std::vector<uint32_t> by_size;
     if (job.paths) {
-        by_size = units_in;
+        by_size.resize(units_in.size());
+        for (size_t i = 0; i < by_size.size(); ++i) by_size[i] = units_in[i];
         std::stable_sort(by_size.begin(), by_size.end(), [&](uint32_t a, uint32_t b) { return job.len[a] > job.len[b]; });
     }
-    const std::vector<uint32_t> &units = job.paths ? by_size : units_in;
+    const UnitList units = job.paths ? UnitList{by_size.data(), 0, by_size.size()} : units_in;
     USE_DEVICE(s.dev);
     Lease lease(s);                       // declared after the device guard: it drains its streams before the device is put back
     int rc = lease.begin(units.size());
@@ -1275,6 +1298,7 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
     size_t ui = 0;            // next unit
     uint64_t consumed = 0;    // bytes of units[ui] already planned
     int batch = 0, prev_bi = -1;
+    uint64_t batch_bytes = 0, total_bytes = 0;
     std::atomic<int> io_err{0};
     std::atomic<size_t> io_idx{(size_t)-1};
 
@@ -1459,6 +1483,10 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
         else rc = launch_lanes(ctx, a, aligned, sk);
         if (rc) return rc;
         CU(cudaEventRecord(s.ev_done[bi], sk));
+        for (size_t i = 0; i < np; ++i) batch_bytes += pieces[i].len;
+        ctx->bytes_staged.fetch_add(batch_bytes);
+        total_bytes += batch_bytes;
+        batch_bytes = 0;
         prev_bi = bi;
         ++batch;
     }
@@ -1487,11 +1515,13 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector
         memcpy(job.out + 16 * (size_t)units[i], h_table + 16 * i, 16 * (j - i));
         i = j;
     }
+    ctx->units_done.fetch_add(nu);
+    ctx->bytes_done.fetch_add(total_bytes);
     return 0;
 }
 
 // Runs one device's share.  (The lease inside run_device_impl drains and returns everything on every path.)
-static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const std::vector<uint32_t> &units) {
+static int run_device(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &units) {
     return run_device_impl(ctx, s, job, units);
 }
 
@@ -1499,31 +1529,43 @@ static int run_job(tpimd5_ctx *ctx, Job &job) {
     if (job.n == 0) return 0;
     if (job.n > 0xffffffffull) return fail(TPIMD5_ERANGE, "more than 2^32 units in one call");
     const int ndev = (int)ctx->slots.size();
-    std::vector<std::vector<uint32_t>> shards;
-    if (ndev == 1 || job.init_states) {
+    struct Count {
+        tpimd5_ctx *c;
+        explicit Count(tpimd5_ctx *x) : c(x) { c->calls_started.fetch_add(1); }
+        ~Count() { c->calls_finished.fetch_add(1); }
+    } count(ctx);
+    if (ndev == 1 || job.init_states)
         // chained units (streams) stay on device 0: their state lives there between calls
-        shard_lpt(job.len, job.n, 1, shards);
-        return run_device(ctx, *ctx->slots[0], job, shards[0]);
-    }
+        return run_device(ctx, *ctx->slots[0], job, UnitList{nullptr, 0, job.n});
     // Unless the sizes are heavy-tailed, cut the caller's order into ndev runs of equal bytes: every device
-    // then gets one dense stretch of the caller's buffer (direct copies, no packing) and the imbalance is at
-    // most one unit.  A unit bigger than a quarter of a device's share means the tail matters: greedy LPT.
+    // then gets one dense stretch of the caller's buffer (direct copies, no packing, no index list) and the
+    // imbalance is at most one unit.  A unit bigger than a quarter of a device's share means the tail matters:
+    // greedy LPT.
     uint64_t total = 0, biggest = 0;
     for (size_t i = 0; i < job.n; ++i) { total += job.len[i] + 72; biggest = std::max(biggest, job.len[i]); }
+    std::vector<UnitList> shards(ndev);
+    std::vector<std::vector<uint32_t>> lists;
     if (biggest <= total / (4 * (uint64_t)ndev)) {
-        shards.assign(ndev, {});
         uint64_t acc = 0;
+        size_t first = 0;
         int d = 0;
         for (size_t i = 0; i < job.n; ++i) {
-            while (d + 1 < ndev && acc >= (total / ndev) * (uint64_t)(d + 1)) ++d;
-            shards[d].push_back((uint32_t)i);
+            if (d + 1 < ndev && acc >= (total / ndev) * (uint64_t)(d + 1)) {
+                shards[d] = UnitList{nullptr, (uint32_t)first, i - first};
+                first = i;
+                ++d;
+            }
             acc += job.len[i] + 72;
         }
+        shards[d] = UnitList{nullptr, (uint32_t)first, job.n - first};
     } else {
-        shard_lpt(job.len, job.n, ndev, shards);
+        shard_lpt(job.len, job.n, ndev, lists);
         // direct mode wants ascending addresses; LPT order is by size.  Re-sort each shard by the
         // caller's order (for files that is listing order, which is also friendliest to the page cache).
-        for (auto &v : shards) std::sort(v.begin(), v.end());
+        for (int d = 0; d < ndev; ++d) {
+            std::sort(lists[d].begin(), lists[d].end());
+            shards[d] = UnitList{lists[d].data(), 0, lists[d].size()};
+        }
     }
     std::vector<int> rcs(ndev, 0);
     std::vector<std::string> errs(ndev);

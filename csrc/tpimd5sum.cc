@@ -17,6 +17,7 @@
 #include <cstring>
 #include <string>
 #include <sys/stat.h>
+#include <unistd.h>
 #include <vector>
 
 #include "../include/tpimd5.h"
@@ -79,8 +80,10 @@ int main(int argc, char **argv) {
                 tpimd5_manifest_entry(m, i, &p, nullptr, nullptr, d, &has);
                 if (has) print_line(d, p);
             }
-        } else if (tpimd5_manifest_load(old_file, &old) != 0) status = die("load");
-        else {
+        } else if (access(old_file, F_OK) != 0 ? tpimd5_manifest_from_arrays(nullptr, nullptr, nullptr, nullptr, nullptr, 0, &old) != 0
+                                               : tpimd5_manifest_load(old_file, &old) != 0) {
+            status = die("load");      // (no old manifest yet -- the loop's first turn -- counts as an empty one: everything is new)
+        } else {
             const size_t n = tpimd5_manifest_count(m);
             std::vector<uint8_t> act(n + 1);
             size_t nt = 0, gone = 0;

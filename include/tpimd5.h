@@ -56,6 +56,17 @@ TPIMD5_API int tpimd5_device_count(void);
 TPIMD5_API int tpimd5_init(const int *device_ids, int n_devices, size_t staging_bytes_per_device, tpimd5_ctx **out);
 TPIMD5_API void tpimd5_destroy(tpimd5_ctx *ctx);
 TPIMD5_API int tpimd5_ctx_devices(const tpimd5_ctx *ctx);
+/* Progress of the context's host-pointer calls since tpimd5_init, for a reporter like the reference's
+ * `progress` goroutine (storage.go:188-211: a stats line every 10 s while a Transfer runs; its counters are
+ * process-global in rclone, here they belong to the context).  Monotonic; poll from any thread at any time:
+ * bytes_staged grows batch by batch while a call is running (bytes handed to the GPU), bytes_done and
+ * units_done when a call returns its digests. */
+typedef struct tpimd5_progress {
+    uint64_t calls_started, calls_finished;
+    uint64_t units_done;
+    uint64_t bytes_staged, bytes_done;
+} tpimd5_progress;
+TPIMD5_API int tpimd5_get_progress(const tpimd5_ctx *ctx, tpimd5_progress *out);
 TPIMD5_API const char *tpimd5_last_error(void);
 TPIMD5_API const char *tpimd5_version(void);
 

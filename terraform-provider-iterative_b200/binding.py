@@ -17,7 +17,7 @@ _lib: Optional[C.CDLL] = None
 
 # every symbol include/tpimd5.h declares (tests check the built library exports each one)
 EXPORTS = [
-    "tpimd5_device_count", "tpimd5_init", "tpimd5_destroy", "tpimd5_ctx_devices", "tpimd5_last_error",
+    "tpimd5_device_count", "tpimd5_init", "tpimd5_destroy", "tpimd5_ctx_devices", "tpimd5_get_progress", "tpimd5_last_error",
     "tpimd5_version", "tpimd5_hash_buffers", "tpimd5_hash_files", "tpimd5_s3_part_size", "tpimd5_s3_nparts",
     "tpimd5_s3_etag_buffer", "tpimd5_s3_etag_file", "tpimd5_s3_plan_parts", "tpimd5_s3_upload_plan", "tpimd5_stream_open", "tpimd5_stream_write",
     "tpimd5_stream_write_many", "tpimd5_stream_sum", "tpimd5_stream_reset", "tpimd5_stream_close", "tpimd5_diff",
@@ -57,6 +57,7 @@ def load_library() -> C.CDLL:
         "tpimd5_init": (i32, [vp, i32, sz, C.POINTER(vp)]),
         "tpimd5_destroy": (None, [vp]),
         "tpimd5_ctx_devices": (i32, [vp]),
+        "tpimd5_get_progress": (i32, [vp, vp]),
         "tpimd5_last_error": (C.c_char_p, []),
         "tpimd5_version": (C.c_char_p, []),
         "tpimd5_hash_buffers": (i32, [vp, vp, vp, vp, sz, vp]),
@@ -371,6 +372,12 @@ class Context:
         _check(self._L.tpimd5_dev_int_probe(self._h, slot, mode, ctas_per_sm, iters, _ptr(d_out), C.byref(blocks),
                                             _ptr(stream)))
         return int(blocks.value)
+
+    def progress(self) -> dict:
+        """Counters of the context's host-pointer calls so far (what a 10 s stats reporter polls)."""
+        buf = (C.c_uint64 * 5)()
+        _check(self._L.tpimd5_get_progress(self._h, buf))
+        return dict(zip(("calls_started", "calls_finished", "units_done", "bytes_staged", "bytes_done"), (int(x) for x in buf)))
 
     def launch_count(self) -> int:
         return int(self._L.tpimd5_launch_count(self._h))

@@ -1,6 +1,7 @@
 """GPU tests of the callers either side of the hash: manifest scan, transfer plan, and
 machine.Transfer for local directories -- the latter written like the reference's own
 TestTransferExcludes (/root/reference/task/common/machine/storage_test.go:55-101)."""
+import hashlib
 import os
 
 import numpy as np
@@ -224,3 +225,58 @@ def test_cli_prints_what_md5sum_prints_and_detects_changes(tmp_path):
     open(os.path.join(root, "zz_new.bin"), "wb").write(b"new")
     r = subprocess.run([CLI, "--changed", man, root, "-x", "**.txt"], capture_output=True, text=True)
     assert r.returncode == 1 and sorted(r.stdout.splitlines()) == sorted([f"* {victim}", "+ zz_new.bin"])
+
+
+@pytest.mark.skipif(not os.path.exists(CLI), reason="tpimd5sum not built")
+def test_cli_changed_without_an_old_manifest_is_the_loops_first_turn(tmp_path):
+    """The patched VM loop (integration/machine-script.sh.tpl.patch) calls `tpimd5sum --changed OLD DIR -o OLD`
+    every 10 s; on the first turn OLD does not exist: everything is new (exit 1, sync runs) and the manifest is
+    written, so the second turn over an unchanged tree exits 0."""
+    import subprocess
+    root = str(tmp_path / "data")
+    files = build_workdir(root, 66, n=12)
+    man = str(tmp_path / "state.tpim")
+    r = subprocess.run([CLI, "--changed", man, root, "-o", man], capture_output=True, text=True)
+    assert r.returncode == 1 and os.path.exists(man), r.stderr
+    o = oracle.FilterSet(oracle.transfer_rules([]))
+    assert sorted(r.stdout.splitlines()) == sorted("+ " + p for p in files if o.include_path(p))
+    r = subprocess.run([CLI, "--changed", man, root, "-o", man], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout == ""
+
+
+def test_s3_upload_plan_matches_the_restated_rclone_rule(ctx, tmp_path):
+    """tpimd5_s3_upload_plan against the oracle's restatement of rclone v1.57.0 backend/s3 Object.Update: single
+    PutObject below the cutoff (Content-MD5 = base64 MD5, ETag = hex MD5), multipart at and above it (part size
+    by the growth rule, per-part Content-MD5, Md5chksum, ETag hex(md5(md5s))-N), and --s3-disable-checksum."""
+    import base64
+    cases = [  # (size, chunk_size, upload_cutoff, max_parts)
+        (0, 0, 0, 0), (1, 0, 0, 0), (3 << 20, 1 << 20, 3 << 20, 0), ((3 << 20) - 1, 1 << 20, 3 << 20, 0),
+        ((5 << 20) + 77, 1 << 20, 1 << 20, 3), (40 * 4096 + 5, 4096, 8192, 10000), (1 << 20, 64, 1, 100),
+    ]
+    for k, (size, chunk, cutoff, maxp) in enumerate(cases):
+        data = oracle.synth_bytes(70 + k, 0, size)
+        path = str(tmp_path / f"obj{k}.bin")
+        data.tofile(path)
+        got = ctx.s3_upload_plan(path, size, chunk, cutoff, maxp)
+        want = oracle.s3_upload_plan(data, chunk or (5 << 20), cutoff or (200 << 20), maxp or 10000)
+        assert tpi.s3_plan_parts(size, chunk, cutoff, maxp) == (want["multipart"], want["part_size"], want["nparts"]), (k, got)
+        for key in ("multipart", "part_size", "nparts", "md5", "content_md5", "etag", "part_content_md5"):
+            assert got[key] == want[key], (k, key, got[key], want[key])
+        assert np.array_equal(got["part_md5"], want["part_md5"])
+        assert got["content_md5"] == base64.b64encode(hashlib.md5(data.tobytes()).digest()).decode()
+        if want["multipart"]:
+            lean = ctx.s3_upload_plan(path, size, chunk, cutoff, maxp, no_whole_md5=True)
+            assert lean["md5"] is None and lean["content_md5"] is None and lean["etag"] == want["etag"]
+    # a file that is not the listed size is an error, as everywhere
+    with pytest.raises(tpi.TpiMd5Error):
+        ctx.s3_upload_plan(str(tmp_path / "obj1.bin"), 2)
+
+
+def test_progress_counters_advance_with_the_calls(ctx):
+    before = ctx.progress()
+    buf, off, ln = oracle.synth_packed(71, [100, 5000, 0, 70000], align=16)
+    ctx.hash_buffers(buf, off, ln)
+    after = ctx.progress()
+    assert after["calls_started"] - before["calls_started"] == 1 == after["calls_finished"] - before["calls_finished"]
+    assert after["units_done"] - before["units_done"] == 4
+    assert after["bytes_done"] - before["bytes_done"] == 75100 == after["bytes_staged"] - before["bytes_staged"]
