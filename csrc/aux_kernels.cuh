@@ -10,34 +10,54 @@ namespace tpimd5 {
 // fs/operations checkHashes (reached from /root/reference/task/common/machine/storage.go:158)
 // for two whole manifests of 16-byte digests.  Output: ascending indices of differing rows.
 //
-// Pass 1 counts per 1024-row tile, pass 2 is an exclusive scan of the tile counts (one CTA,
-// the array is n/1024 long), pass 3 recomputes the comparison and scatters.  Within a tile the
-// order comes from ballots: warp w owns rows [128w, 128w+128) as four coalesced 512-byte reads.
-// HBM-bound: 32 B read per row twice; tile counts are the only scratch.
+// Pass 1 compares (each manifest is read ONCE: 32 B per row, the algorithmic traffic), keeps the outcome
+// as one bit per row and counts per 1024-row tile; pass 2 is an exclusive scan of the tile counts (one CTA,
+// the array is n/1024 long); pass 3 scatters from the bitmap alone (n/8 bytes).  Within a tile the order
+// comes from ballots: warp w owns rows [128w, 128w+128) as four coalesced 512-byte reads.
+// HBM-bound; scratch per 1,024-row tile: 8 B of count + 128 B of bitmap (DIFF_SCRATCH_PER_TILE).
 // ---------------------------------------------------------------------------------------------
 constexpr int DIFF_THREADS = 256;
 constexpr int DIFF_K = 4;
 constexpr int DIFF_TILE = DIFF_THREADS * DIFF_K;
+constexpr size_t DIFF_SCRATCH_PER_TILE = sizeof(uint64_t) + DIFF_TILE / 8;
+
+// layout of the scratch: tile counts first, then the bitmap (one uint32 per 32 rows)
+__host__ __device__ inline uint32_t *diff_bitmap(uint64_t *tile_counts, uint64_t tiles) { return (uint32_t *)(tile_counts + tiles); }
 
 template <bool SCATTER>
 __global__ void __launch_bounds__(DIFF_THREADS) diff_tile_kernel(const uint4 *__restrict__ a, const uint4 *__restrict__ b,
                                                                   uint64_t n, uint64_t *__restrict__ tile_counts,
-                                                                  uint32_t *__restrict__ idx_out) {
+                                                                  uint32_t *__restrict__ bitmap, uint32_t *__restrict__ idx_out) {
     __shared__ uint32_t wsum[DIFF_THREADS / 32];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint64_t row0 = (uint64_t)blockIdx.x * DIFF_TILE + warp * (32 * DIFF_K);
     uint32_t bal[DIFF_K];
     uint32_t cnt = 0;
+    if (!SCATTER) {
 #pragma unroll
-    for (int k = 0; k < DIFF_K; ++k) {
-        const uint64_t r = row0 + k * 32 + lane;
-        bool ne = false;
-        if (r < n) {
-            const uint4 x = __ldg(a + r), y = __ldg(b + r);
-            ne = ((x.x ^ y.x) | (x.y ^ y.y) | (x.z ^ y.z) | (x.w ^ y.w)) != 0u;
+        for (int k = 0; k < DIFF_K; ++k) {
+            const uint64_t r = row0 + k * 32 + lane;
+            bool ne = false;
+            if (r < n) {
+                const uint4 x = __ldg(a + r), y = __ldg(b + r);
+                ne = ((x.x ^ y.x) | (x.y ^ y.y) | (x.z ^ y.z) | (x.w ^ y.w)) != 0u;
+            }
+            bal[k] = __ballot_sync(0xffffffffu, ne);
+            cnt += __popc(bal[k]);
         }
-        bal[k] = __ballot_sync(0xffffffffu, ne);
-        cnt += __popc(bal[k]);
+        if (lane < DIFF_K) {                       // the warp's four ballots, one 16-byte store
+            uint32_t v = bal[0];
+#pragma unroll
+            for (int k = 1; k < DIFF_K; ++k) v = lane == (uint32_t)k ? bal[k] : v;
+            bitmap[(row0 >> 5) + lane] = v;
+        }
+    } else {
+        const uint32_t mine = lane < DIFF_K ? bitmap[(row0 >> 5) + lane] : 0u;
+#pragma unroll
+        for (int k = 0; k < DIFF_K; ++k) {
+            bal[k] = __shfl_sync(0xffffffffu, mine, k);
+            cnt += __popc(bal[k]);
+        }
     }
     if (lane == 0) wsum[warp] = cnt;
     __syncthreads();

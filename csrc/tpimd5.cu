@@ -970,9 +970,10 @@ extern "C" int tpimd5_dev_s3_etag(tpimd5_ctx *ctx, int slot, const void *d_data,
 static int diff_launch(tpimd5_ctx *ctx, const void *d_old16, const void *d_new16, size_t n, uint32_t *d_idx,
                        uint64_t *d_count, uint64_t *tile_counts, cudaStream_t st) {
     const uint64_t tiles = (n + DIFF_TILE - 1) / DIFF_TILE;
-    diff_tile_kernel<false><<<(unsigned)tiles, DIFF_THREADS, 0, st>>>((const uint4 *)d_old16, (const uint4 *)d_new16, n, tile_counts, nullptr);
+    uint32_t *bitmap = diff_bitmap(tile_counts, tiles);
+    diff_tile_kernel<false><<<(unsigned)tiles, DIFF_THREADS, 0, st>>>((const uint4 *)d_old16, (const uint4 *)d_new16, n, tile_counts, bitmap, nullptr);
     diff_scan_kernel<<<1, 1024, 0, st>>>(tile_counts, tiles, d_count);
-    diff_tile_kernel<true><<<(unsigned)tiles, DIFF_THREADS, 0, st>>>((const uint4 *)d_old16, (const uint4 *)d_new16, n, tile_counts, d_idx);
+    diff_tile_kernel<true><<<(unsigned)tiles, DIFF_THREADS, 0, st>>>(nullptr, nullptr, n, tile_counts, bitmap, d_idx);
     CU(cudaGetLastError());
     ctx->launches.fetch_add(3);
     return 0;
@@ -996,7 +997,7 @@ extern "C" int tpimd5_dev_diff(tpimd5_ctx *ctx, int slot, const void *d_old16, c
     {
         // tile counts live in the slot's scratch, which calls on this slot share
         std::lock_guard<std::mutex> g(s->scratch_mu);
-        int rc = ensure_scratch(*s, ((n + DIFF_TILE - 1) / DIFF_TILE) * sizeof(uint64_t));
+        int rc = ensure_scratch(*s, ((n + DIFF_TILE - 1) / DIFF_TILE) * DIFF_SCRATCH_PER_TILE);
         if (rc) return rc;
         counts = (uint64_t *)s->d_scratch;
     }
@@ -1790,7 +1791,7 @@ extern "C" int tpimd5_diff(tpimd5_ctx *ctx, const uint8_t *old16, const uint8_t 
             give_stream(s, st);
         }
     } held(s);
-    int rc = take_block(s, b_cnt + 8 + tiles * sizeof(uint64_t), held.blk);
+    int rc = take_block(s, b_cnt + 8 + tiles * DIFF_SCRATCH_PER_TILE, held.blk);
     if (rc == 0) rc = take_stream(s, held.st);
     if (rc) return rc;
     uint8_t *const base = held.blk.d;
