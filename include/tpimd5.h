@@ -233,8 +233,13 @@ TPIMD5_API int tpimd5_transfer_local(tpimd5_ctx *ctx, const char *source, const 
  * the reference has no counterpart (its data is never on a device).
  *   offsets == NULL: unit i is bytes [i*stride, min((i+1)*stride, base_bytes)) (fixed-size
  *   files / S3 parts), with lengths ignored; a 16-byte aligned base and stride take the
- *   TMA-fed kernel.  One unit may hold at most 31 GiB in these calls (TPIMD5_ERANGE beyond);
- *   the host-pointer calls have no such limit, they chain a long unit across launches.
+ *   TMA-fed kernels (throughput kernel for launches that fill the SMs, latency kernel below
+ *   ~57,000 units) and may be of any length: a unit longer than 2 GiB is hashed as a run of
+ *   1 GiB launches on the caller's stream.  Unaligned strided units and units given by
+ *   offset/length arrays may hold at most 31 GiB each (TPIMD5_ERANGE / undefined beyond for
+ *   device arrays the host cannot see).  A caller that knows its listing passes large files
+ *   as single strided units on streams of their own and the rest as one ragged batch
+ *   (bench.py run_c4); the host-pointer calls have no limit, they chain long units themselves.
  *   Scratch: hash_buffers with offset arrays (>= 4,096 units are bucketed by length with a
  *   device radix sort), s3_etag with d_part_digests == NULL, and diff (tile counts) keep their
  *   temporaries in one per-slot buffer that grows on demand (cudaMalloc on first use; an outgrown

@@ -10,6 +10,11 @@ rule and ``equal()`` decision table (reached from
 ``/root/reference/task/common/machine/storage.go:158``), plus pure-Python restatements of the
 small string-level rules (rclone filter globs, md5sum manifest lines).
 
+The rclone rules restated here (``equal``, the S3 part-size growth rule and upload plan, ``md5_from_etag``,
+filter globs and ``glob_to_dir_globs``) come from knowledge of rclone v1.57.0; its source is not on this machine,
+so they are UNVERIFIED against that release: agreement between this package and ``csrc/`` shows the two
+restatements are consistent, nothing more.
+
 Parity status: digest parity is *unpinned by the reference's own tests* (they hold no digest);
 the oracle is pinned on RFC 1321 vectors, hashlib, OpenSSL and coreutils md5sum instead.  The
 file-set membership rules ARE pinned on the reference's ``storage_test.go:55-101`` cases.
