@@ -38,6 +38,7 @@
 #include "md5_lanes.cuh"
 #include "md5_strided_tma.cuh"
 #include "md5_chain_tma.cuh"
+#include "md5_ragged_chain.cuh"
 
 using namespace tpimd5;
 
@@ -555,7 +556,7 @@ extern "C" int tpimd5_get_progress(const tpimd5_ctx *ctx, tpimd5_progress *out) 
 }
 extern "C" uint64_t tpimd5_launch_count(const tpimd5_ctx *ctx) { return ctx ? ctx->launches.load() : 0; }
 extern "C" int tpimd5_set_variant(tpimd5_ctx *ctx, int variant) {
-    if (!ctx || variant < 0 || variant > 499) return fail(TPIMD5_EINVAL, "tpimd5_set_variant: 100*loader(0 cp.async, 2 tensor map for strided units, 3 / 4 latency kernel for strided units, 2 / 4 blocks per iteration) + 10*mode(0,4,6) + shape");
+    if (!ctx || variant < 0 || variant > 599) return fail(TPIMD5_EINVAL, "tpimd5_set_variant: 100*loader(0 cp.async, 2 tensor map for strided units, 3 / 4 latency kernel for strided units, 2 / 4 blocks per iteration, 5 ragged latency kernel) + 10*mode(0,4,6) + shape");
     ctx->variant = variant;
     return 0;
 }
@@ -807,12 +808,45 @@ static void decode_variant(int v, int &loader, int &mode, int &shape) {
     loader = v / 100; mode = (v / 10) % 10; shape = v % 10;
 }
 
+template <int WARPS, int MINB, int NSTAGE, int SB, int MODE>
+static int launch_ragged_chain_cfg(const LaneArgs &a, cudaStream_t st) {
+    using Cfg = RaggedCfg<WARPS, NSTAGE, SB>;
+    auto kern = md5_ragged_chain_kernel<WARPS, MINB, NSTAGE, SB, MODE, 4>;
+    static ConfiguredSet configured;
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    if (!configured.has(dev)) {
+        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+        CU(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        configured.add(dev);
+    }
+    const uint64_t per_cta = WARPS * 32;
+    const uint64_t grid = (a.n + per_cta - 1) / per_cta;
+    kern<<<(unsigned)grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(a);
+    CU(cudaGetLastError());
+    return 0;
+}
+
 // `aligned`: every unit starts on a 16-byte boundary of device memory.
 static int launch_lanes(tpimd5_ctx *ctx, const LaneArgs &a0, bool aligned, cudaStream_t st) {
     if (a0.n == 0) return 0;
     LaneArgs a = a0;
     int loader, mode, shape;
     decode_variant(ctx->variant.load(), loader, mode, shape);
+    // A ragged batch with too few chains to fill the SMs (a workdir of a few hundred files of all sizes): the
+    // ragged latency kernel (md5_ragged_chain.cuh).  It needs per-unit offset/length arrays and 16-byte aligned
+    // units, which is what the host pipeline's packer produces.  Variant 500 + x forces it for tests.
+    const uint64_t warps = (a.n + 31) / 32;
+    if ((ctx->variant.load() == 0 || loader == 5) && aligned && a.off && a.len && warps <= (uint64_t)148 * 12) {
+        int rc;
+        if (loader == 5 && shape == 2) rc = launch_ragged_chain_cfg<4, 3, 2, 256, 4>(a, st);
+        else if (loader == 5 && shape == 3) rc = launch_ragged_chain_cfg<4, 3, 2, 256, 6>(a, st);
+        else if (loader == 5 || warps <= 592) rc = launch_ragged_chain_cfg<4, 1, 2, 512, 4>(a, st);
+        else if (warps <= 888) rc = launch_ragged_chain_cfg<4, 3, 2, 256, 4>(a, st);
+        else rc = launch_ragged_chain_cfg<4, 3, 2, 256, 6>(a, st);
+        if (rc == 0) ctx->launches.fetch_add(1);
+        return rc;
+    }
     // library default: too few chains to fill the SMs -> the formulation with the shortest dependent
     // chain (mode 4); enough of them -> the one that spreads the additions over both integer pipes (6)
     if (ctx->variant.load() == 0 && a.n < (uint64_t)148 * 16 * 32) { mode = 4; shape = 2; }   // + 256-byte stages: half the per-stage work
@@ -1138,6 +1172,7 @@ struct Lease {
     cudaStream_t stream = nullptr;
     std::vector<int> bufs;      // staging buffers held, in the order they will be reused
     size_t next = 0;            // index in bufs of the oldest batch in flight
+    int share_seen = NBUF;      // staging buffers this call may hold, as of its last acquire
     bool counted = false;
     explicit Lease(Slot &slot) : s(slot) {}
     Lease(const Lease &) = delete;
@@ -1164,6 +1199,7 @@ struct Lease {
                 std::unique_lock<std::mutex> lk(s.mu);
                 for (;;) {
                     const int share = std::max(1, NBUF / std::max(1, s.active_calls));
+                    share_seen = share;
                     if ((int)bufs.size() < share && s.n_free > 0) {
                         for (int i = 0; i < NBUF; ++i)
                             if (s.buf_free[i]) {
@@ -1314,6 +1350,13 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
         if (rc) return rc;
         const double tr_b0 = trace_now();
         // ---- plan one batch --------------------------------------------------------------------
+        // The first batches are short (32, 64, 128 MiB, then whole buffers): units are taken longest first, so
+        // the longest chains -- which bound the whole call -- start a few milliseconds after the call does
+        // instead of after a full buffer has been read and copied.
+        // (Only while the call has the device to itself: with other calls active every call is down to a few
+        // buffers, and more, shorter batches would just make it wait for its own kernels more often.)
+        const uint64_t cap = lease.share_seen < NBUF ? s.stage_bytes
+                                                     : std::min<uint64_t>(s.stage_bytes, ((uint64_t)32 << 20) << std::min(batch, 3));
         pieces.clear();
         uint64_t used = 0;       // bytes of staging consumed
         uint64_t lo = 0;         // direct mode: caller offset of the batch's first byte ...
@@ -1331,8 +1374,8 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
             } else {
                 dst = (used + 15) & ~(uint64_t)15;
             }
-            if (dst > s.stage_bytes) break;
-            const uint64_t space = s.stage_bytes - dst;
+            if (dst > cap) break;
+            const uint64_t space = cap - dst;
             if (rem + (from_files ? 1 : 0) <= space) {
                 pieces.push_back({(uint32_t)ui, consumed, rem, dst, true});
                 used = dst + rem + (from_files ? 1 : 0);      // files: one spare byte for the grew-since-listing probe
