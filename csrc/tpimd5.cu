@@ -1586,7 +1586,21 @@ static int run_job(tpimd5_ctx *ctx, Job &job) {
     // imbalance is at most one unit.  A unit bigger than a quarter of a device's share means the tail matters:
     // greedy LPT.
     uint64_t total = 0, biggest = 0;
-    for (size_t i = 0; i < job.n; ++i) { total += job.len[i] + 72; biggest = std::max(biggest, job.len[i]); }
+    {
+        // (millions of units: summed by the pool, 64 Ki units per item)
+        constexpr size_t CHUNK = 1u << 16;
+        std::atomic<uint64_t> a_total{0}, a_big{0};
+        std::function<void(size_t)> sum = [&](size_t c) {
+            uint64_t t = 0, b = 0;
+            const size_t hi = std::min(job.n, (c + 1) * CHUNK);
+            for (size_t i = c * CHUNK; i < hi; ++i) { t += job.len[i] + 72; b = std::max(b, job.len[i]); }
+            a_total.fetch_add(t);
+            uint64_t cur = a_big.load();
+            while (b > cur && !a_big.compare_exchange_weak(cur, b)) {}
+        };
+        ctx->pool->parallel_for((job.n + CHUNK - 1) / CHUNK, 1, sum);
+        total = a_total.load(); biggest = a_big.load();
+    }
     std::vector<UnitList> shards(ndev);
     std::vector<std::vector<uint32_t>> lists;
     if (biggest <= total / (4 * (uint64_t)ndev)) {
