@@ -409,7 +409,7 @@ def run_c2(env):
     if os.path.exists(tpath):
         try:
             t = json.load(open(tpath))
-            if t.get("kernel") == "md5_strided_tma_kernel" and t.get("algorithmic_bytes_per_launch") == nbytes and \
+            if t.get("kernel") == "md5_chain_tma_kernel<4,6,2,1,6,2>" and t.get("algorithmic_bytes_per_launch") == nbytes and \
                     t.get("kernel_variant", 0) == args.variant:
                 traffic = t.get("dram_bytes_per_launch")
         except Exception:
@@ -421,7 +421,7 @@ def run_c2(env):
         "config": c2_config(args),
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": env.peak, "unit": "GB/s",
                      "frac": round(achieved / env.peak, 4), "traffic": traffic, "peak_source": env.peak_src,
-                     "kernel": "md5_strided_tma_kernel (K1, one lane per file, TMA-fed)", "algorithmic_bytes_per_launch": nbytes,
+                     "kernel": "md5_chain_tma_kernel<4,6,2,1,6,2> (K1, one lane per file, producer warp + TMA)", "algorithmic_bytes_per_launch": nbytes,
                      "int_issue_peak_GBps": round(int_peak, 1), "frac_of_int_issue": round(achieved / int_peak, 4),
                      "int_issue_source": f"register-only probe of the same 64-step MD5 body (best step formulation: mode {int_peak_mode}), 32 warps/SM, same run",
                      "sustained": sustained},

@@ -59,8 +59,16 @@ struct ChainCfg {
 
 template <int WARPS, int MINB, int NSTAGE, int TILES, int MODE, int U = 2>
 __global__ void __launch_bounds__((WARPS + 1) * 32, MINB)
-md5_chain_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uint32_t unit_len, uint4 *__restrict__ table,
-                     uint64_t prior, uint32_t flags) {
+md5_chain_tma_kernel(const __grid_constant__ CUtensorMap tmap_main, uint64_t n_main, uint32_t unit_len_main, uint4 *__restrict__ table_main,
+                     uint64_t prior, uint32_t flags, const __grid_constant__ CUtensorMap tmap_tail, uint32_t tail_len) {
+    // The buffer's end usually cuts the last unit short (the last part of an S3 object).  That unit cannot be a row
+    // of the main tensor (its row would reach past the buffer), so it is a tensor of its own, hashed by one extra
+    // CTA of the SAME launch (the last one): it runs next to the others instead of after them.
+    const bool is_tail = tail_len != 0u && blockIdx.x == gridDim.x - 1u;
+    const CUtensorMap *const tmap = is_tail ? &tmap_tail : &tmap_main;
+    const uint64_t n = is_tail ? 1u : n_main;
+    const uint32_t unit_len = is_tail ? tail_len : unit_len_main;
+    uint4 *const table = is_tail ? table_main + n_main : table_main;
     using Cfg = ChainCfg<WARPS, NSTAGE, TILES>;
     constexpr uint32_t SB = 128u * TILES;                      // bytes of one unit per stage
     constexpr uint32_t BPS = 2u * TILES;                       // MD5 blocks per stage
@@ -69,7 +77,7 @@ md5_chain_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uint3
     extern __shared__ uint8_t smem_raw[];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);     // warp-uniform by construction
-    const uint64_t cta_u0 = (uint64_t)blockIdx.x * (WARPS * 32u);
+    const uint64_t cta_u0 = is_tail ? 0u : (uint64_t)blockIdx.x * (WARPS * 32u);
 
     const uint32_t sbase = ((uint32_t)__cvta_generic_to_shared(smem_raw) + 1023u) & ~1023u;   // swizzled boxes: 1 KiB aligned
     const uint32_t bars = sbase + Cfg::DATA_BYTES;             // full[w][s] then empty[w][s]
@@ -102,7 +110,7 @@ md5_chain_tma_kernel(const __grid_constant__ CUtensorMap tmap, uint64_t n, uint3
                 const uint32_t dst = sbase + w * Cfg::WARP_BYTES + buf * Cfg::STAGE_BYTES;
 #pragma unroll
                 for (int t = 0; t < TILES; ++t)                // a box wholly past unit_len (or past n) arrives as zeros
-                    tma_load_2d(dst + t * Cfg::TILE_BYTES, &tmap, (k * TILES + t) << 7, (uint32_t)(cta_u0 + w * 32u), full);
+                    tma_load_2d(dst + t * Cfg::TILE_BYTES, tmap, (k * TILES + t) << 7, (uint32_t)(cta_u0 + w * 32u), full);
             }
         }
         return;

@@ -314,6 +314,7 @@ struct Slot {
     bool buf_free[NBUF];
     int n_free = NBUF;
     int active_calls = 0;                // host calls that hold a lease on this slot right now
+    int starving = 0;                    // ... of which are waiting for a first staging buffer
     // free lists, kept until tpimd5_destroy
     std::vector<TableBuf> free_tables;
     std::vector<DevBlock> free_blocks;
@@ -664,24 +665,41 @@ static int launch_tma_cfg(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len
     return 0;
 }
 
-template <int WARPS, int MINB, int NSTAGE, int TILES, int MODE, int U = 2>
-static int launch_chain_cfg(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len, uint4 *table, cudaStream_t st,
-                            uint64_t prior = 0, uint32_t flags = LANE_FINAL) {
+// Shared-memory attributes of one instantiation of the producer-warp kernel, for the device that is current.
+template <int WARPS, int MINB, int NSTAGE, int TILES, int MODE, int U>
+static int configure_chain() {
     using Cfg = ChainCfg<WARPS, NSTAGE, TILES>;
     auto kern = md5_chain_tma_kernel<WARPS, MINB, NSTAGE, TILES, MODE, U>;
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    return 0;
+}
+
+// The launch alone (the instantiation must have been configured on this device).
+template <int WARPS, int MINB, int NSTAGE, int TILES, int MODE, int U>
+static int enqueue_chain(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len, uint4 *table, cudaStream_t st, uint64_t prior,
+                         uint32_t flags, const CUtensorMap *tail = nullptr, uint32_t tail_len = 0) {
+    using Cfg = ChainCfg<WARPS, NSTAGE, TILES>;
+    const uint64_t per_cta = WARPS * 32;
+    const uint64_t grid = (n + per_cta - 1) / per_cta + (tail && tail_len ? 1 : 0);   // + one CTA for a ragged last unit (table[n])
+    md5_chain_tma_kernel<WARPS, MINB, NSTAGE, TILES, MODE, U><<<(unsigned)grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(
+        tmap, n, unit_len, table, prior, flags, tail && tail_len ? *tail : tmap, tail ? tail_len : 0u);
+    CU(cudaGetLastError());
+    return 0;
+}
+
+template <int WARPS, int MINB, int NSTAGE, int TILES, int MODE, int U = 2>
+static int launch_chain_cfg(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len, uint4 *table, cudaStream_t st,
+                            uint64_t prior = 0, uint32_t flags = LANE_FINAL, const CUtensorMap *tail = nullptr, uint32_t tail_len = 0) {
     static ConfiguredSet configured;
     int dev = 0;
     CU(cudaGetDevice(&dev));
     if (!configured.has(dev)) {
-        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-        CU(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        int rc = configure_chain<WARPS, MINB, NSTAGE, TILES, MODE, U>();
+        if (rc) return rc;
         configured.add(dev);
     }
-    const uint64_t per_cta = WARPS * 32;
-    const uint64_t grid = (n + per_cta - 1) / per_cta;
-    kern<<<(unsigned)grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(tmap, n, unit_len, table, prior, flags);
-    CU(cudaGetLastError());
-    return 0;
+    return enqueue_chain<WARPS, MINB, NSTAGE, TILES, MODE, U>(tmap, n, unit_len, table, st, prior, flags, tail, tail_len);
 }
 
 // The latency kernel (md5_chain_tma.cuh) in one of its shapes; mode 4 unless 0 or 6 is asked for; U blocks
@@ -712,12 +730,15 @@ static bool chain_launch_fits(uint64_t n) { return (n + 31) / 32 <= (uint64_t)14
 
 // The latency kernel in the shape that suits the launch's warp count (see launch_strided_tma).
 static int launch_chain_default(const CUtensorMap &tmap, uint64_t n, uint32_t ul, uint4 *table, cudaStream_t st, uint64_t prior,
-                                uint32_t flags) {
+                                uint32_t flags, const CUtensorMap *tail = nullptr, uint32_t tail_len = 0) {
     const uint64_t warps = (n + 31) / 32;
-    if (warps <= 148) return launch_chain_cfg<2, 2, 4, 2, 4, 4>(tmap, n, ul, table, st, prior, flags);
-    if (warps <= 592) return launch_chain_cfg<4, 1, 2, 4, 4, 4>(tmap, n, ul, table, st, prior, flags);
-    if (warps <= 888) return launch_chain_cfg<3, 1, 2, 4, 4, 4>(tmap, n, ul, table, st, prior, flags);
-    return launch_chain_cfg<4, 3, 2, 2, 6, 4>(tmap, n, ul, table, st, prior, flags);
+    if (warps <= 148) return launch_chain_cfg<2, 2, 4, 2, 4, 4>(tmap, n, ul, table, st, prior, flags, tail, tail_len);
+    if (warps <= 592) return launch_chain_cfg<4, 1, 2, 4, 4, 4>(tmap, n, ul, table, st, prior, flags, tail, tail_len);
+    if (warps <= 888) return launch_chain_cfg<3, 1, 2, 4, 4, 4>(tmap, n, ul, table, st, prior, flags, tail, tail_len);
+    if (warps <= (uint64_t)148 * 12) return launch_chain_cfg<4, 3, 2, 2, 6, 4>(tmap, n, ul, table, st, prior, flags, tail, tail_len);
+    // enough chains to fill the SMs: the integer pipes are the limit -- 4 hashing warps + the producer per CTA, six
+    // CTAs per SM (24 hashing warps), one box per stage, step mode 6 (the additions spread over both integer pipes)
+    return launch_chain_cfg<4, 6, 2, 1, 6, 2>(tmap, n, ul, table, st, prior, flags, tail, tail_len);
 }
 
 static int encode_rows(CUtensorMap *tmap, const void *base, uint64_t row_bytes, uint64_t rows, uint64_t pitch) {
@@ -750,11 +771,20 @@ static int launch_long_units(tpimd5_ctx *ctx, const void *base, uint64_t stride,
 }
 
 // n units of unit_len bytes, unit u at base + u*stride.  shape: 1..4, mode 0 or 4.
+// tail_len != 0: the unit after the n whole ones, cut short by the buffer's end (it starts at base + n*stride), goes
+// into the same launch and its digest to table[n] -- default kernel choice only.
 static int launch_strided_tma(tpimd5_ctx *ctx, const void *base, uint64_t stride, uint64_t unit_len, uint64_t n, uint4 *table,
-                              int loader, int shape, int mode, cudaStream_t st) {
-    CUtensorMap tmap;
+                              int loader, int shape, int mode, cudaStream_t st, uint64_t tail_len = 0) {
+    CUtensorMap tmap, tail;
     if (int rc0 = encode_rows(&tmap, base, unit_len, n, stride)) return rc0;
+    if (tail_len)
+        if (int rc0 = encode_rows(&tail, (const uint8_t *)base + n * stride, tail_len, 1, (tail_len + 15) & ~(uint64_t)15)) return rc0;
     int rc;
+    if (tail_len) {
+        rc = launch_chain_default(tmap, n, (uint32_t)unit_len, table, st, 0, LANE_FINAL, &tail, (uint32_t)tail_len);
+        if (rc == 0) ctx->launches.fetch_add(1);
+        return rc;
+    }
     if (loader >= 3) {
         rc = loader == 3 ? launch_chain<2>(tmap, n, (uint32_t)unit_len, table, shape, mode, st)
                          : launch_chain<4>(tmap, n, (uint32_t)unit_len, table, shape, mode, st);
@@ -773,11 +803,13 @@ static int launch_strided_tma(tpimd5_ctx *ctx, const void *base, uint64_t stride
     //                            the integer pipes start to bind: the step formulation that splits the adds (6)
     // Beyond that (12 warps per SM would no longer hold the launch in one wave) the throughput kernel below.
     // All with four blocks per loop iteration.
-    if (shape == 0 && chain_launch_fits(n)) {
+    // Beyond that the same kernel in its throughput shape (see launch_chain_default).
+    if (shape == 0) {
         rc = launch_chain_default(tmap, n, (uint32_t)unit_len, table, st, 0, LANE_FINAL);
         if (rc == 0) ctx->launches.fetch_add(1);
         return rc;
     }
+    // explicit shapes of round 1's self-issuing kernel (md5_strided_tma.cuh), kept for comparison sweeps
 #define TPI_TMA(M)                                                                          \
     switch (shape) {                                                                        \
         case 1: rc = launch_tma_cfg<4, 4, 3, M>(tmap, n, (uint32_t)unit_len, table, st); break;  \
@@ -881,6 +913,9 @@ static int launch_strided(tpimd5_ctx *ctx, const void *base, uint64_t base_bytes
     decode_variant(ctx->variant.load(), loader, mode, shape);
     const uint64_t n_full = std::min<uint64_t>(n, base_bytes / stride);
     if (loader >= 2 && n_full && tma_layout_ok(base, stride, n_full) && (stride <= ctx->row_max || chain_launch_fits(n_full))) {
+        const uint64_t tail = base_bytes - n_full * stride;       // bytes of the unit the buffer's end cuts short
+        if (ctx->variant.load() == 0 && stride <= ctx->row_max && n == n_full + 1 && tail >= 1)
+            return launch_strided_tma(ctx, base, stride, stride, n_full, table, loader, shape, mode, st, tail);   // one launch for both
         int rc = stride <= ctx->row_max ? launch_strided_tma(ctx, base, stride, stride, n_full, table, loader, shape, mode, st)
                                        : launch_long_units(ctx, base, stride, stride, n_full, table, st);
         if (rc || n_full == n) return rc;
@@ -1187,53 +1222,60 @@ struct Lease {
         if (rc) return rc;
         return take_stream(s, stream);
     }
-    // A staging buffer for the next batch.  While the call is alone on the device it may draw all NBUF; with
-    // other calls in flight it stays within its share (NBUF / calls, at least one) and hands its surplus
-    // back as those batches drain.  At its limit the call recycles its own oldest buffer (waiting for that
-    // batch's kernel); a call that holds none waits for one to come back -- a call that holds some never
-    // does, so calls cannot block each other.
-    int acquire(int &bi_out) {
+    // A staging buffer for the next batch.  A call may draw a free buffer while it is within its share (NBUF /
+    // calls, at least one) or while more are free than there are calls that hold none at all; otherwise it reuses
+    // its own oldest buffer as soon as that batch's kernel has finished (polled, so that a buffer freed by ANOTHER
+    // call in the meantime is taken instead of waiting out a long chain of its own), handing it back instead if
+    // it is over its share and someone is starving.  A call that holds nothing waits for a buffer to come back.
+    int acquire(int &bi_out, bool need_host) {
+        std::unique_lock<std::mutex> lk(s.mu);
+        bool starving = false;
         for (;;) {
-            bool shed = false;
-            {
-                std::unique_lock<std::mutex> lk(s.mu);
-                for (;;) {
-                    const int share = std::max(1, NBUF / std::max(1, s.active_calls));
-                    share_seen = share;
-                    if ((int)bufs.size() < share && s.n_free > 0) {
-                        for (int i = 0; i < NBUF; ++i)
-                            if (s.buf_free[i]) {
-                                s.buf_free[i] = false;
-                                --s.n_free;
-                                bufs.insert(bufs.begin() + next, i);   // in front of the oldest: it is the newest now
-                                ++next;
-                                if (next >= bufs.size()) next = 0;
-                                bi_out = i;
-                                return 0;
-                            }
-                    }
-                    if (!bufs.empty()) {
-                        shed = (int)bufs.size() > share;    // others have arrived: hand the surplus back as it drains
-                        break;
-                    }
-                    s.cv.wait(lk);
-                }
-            }
-            const int bi = bufs[next];
-            CU(cudaEventSynchronize(s.ev_done[bi]));
-            if (!shed) {
-                next = (next + 1) % bufs.size();
-                bi_out = bi;
+            const int share = std::max(1, NBUF / std::max(1, s.active_calls));
+            share_seen = share;
+            if (s.n_free > 0 && (bufs.empty() || (int)bufs.size() < share || s.n_free > s.starving)) {
+                // prefer a buffer whose memory exists already: allocating 256 MiB of pinned memory takes tens of
+                // milliseconds and stalls every other CUDA call of the process while it runs
+                int pick = -1;
+                for (int pass = 0; pass < 3 && pick < 0; ++pass)
+                    for (int i = 0; i < NBUF && pick < 0; ++i)
+                        if (s.buf_free[i] && (pass == 2 || (s.d_stage[i] && (pass == 1 || !need_host || s.h_stage[i])))) pick = i;
+                s.buf_free[pick] = false;
+                --s.n_free;
+                if (starving) --s.starving;
+                bufs.insert(bufs.begin() + next, pick);        // in front of the oldest: it is the newest now
+                ++next;
+                if (next >= bufs.size()) next = 0;
+                bi_out = pick;
                 return 0;
             }
-            bufs.erase(bufs.begin() + next);
-            if (next >= bufs.size()) next = 0;
-            {
-                std::lock_guard<std::mutex> g(s.mu);
-                s.buf_free[bi] = true;
-                ++s.n_free;
+            if (!bufs.empty()) {
+                const int bi = bufs[next];
+                lk.unlock();
+                const cudaError_t q = cudaEventQuery(s.ev_done[bi]);
+                lk.lock();
+                if (q == cudaSuccess) {
+                    if ((int)bufs.size() > share && s.starving > 0) {      // over the share while someone has nothing: hand it back
+                        bufs.erase(bufs.begin() + next);
+                        if (next >= bufs.size()) next = 0;
+                        s.buf_free[bi] = true;
+                        ++s.n_free;
+                        s.cv.notify_all();
+                        continue;
+                    }
+                    next = (next + 1) % bufs.size();
+                    bi_out = bi;
+                    return 0;
+                }
+                if (q != cudaErrorNotReady) {
+                    lk.unlock();
+                    return fail(TPIMD5_ECUDA, "cudaEventQuery: %s", cudaGetErrorString(q));
+                }
+            } else if (!starving) {
+                starving = true;
+                ++s.starving;
             }
-            s.cv.notify_all();
+            s.cv.wait_for(lk, std::chrono::microseconds(200));
         }
     }
     ~Lease() {
@@ -1343,7 +1385,7 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
         // ---- a staging buffer: a fresh one, or this call's oldest once its batch has been consumed ----
         const double tr_w0 = trace_now();
         int bi = -1;
-        rc = lease.acquire(bi);
+        rc = lease.acquire(bi, !direct);
         if (rc) return rc;
         tr_wait += trace_now() - tr_w0;
         rc = ensure_buffer(ctx, s, bi, !direct);
@@ -2041,6 +2083,8 @@ extern "C" int tpimd5_dev_s3_etag_noalloc(int device, const void *d_data, uint64
             if (!ptr) return fail(TPIMD5_ECUDA, "s3_etag_noalloc: no device address for the scratch array on device %d", device);
             int rc = configure_lanes<256, true, 4, 3, 4>();
             if (rc == 0) rc = configure_lanes<256, false, 4, 3, 4>();
+            if (rc == 0) rc = configure_chain<2, 2, 4, 2, 4, 4>();
+            if (rc == 0) rc = configure_chain<4, 1, 2, 4, 4, 4>();
             if (rc) return rc;
             g_noalloc_dev_ptr[device] = ptr;
         }
@@ -2049,18 +2093,46 @@ extern "C" int tpimd5_dev_s3_etag_noalloc(int device, const void *d_data, uint64
 
     cudaStream_t st = (cudaStream_t)cuda_stream;
     // At most 10,000 chains: far too few to fill the SMs, so every chain runs at its dependent-op latency.
-    // Same choice as launch_lanes makes for such launches: 256-byte stages and the step formulation with
-    // the shortest dependent chain (mode 4).
+    // Parts that the TMA unit can address (16-byte aligned data and part size, at most 2 GiB per part) take the
+    // latency kernel in the two shapes tpimd5_dev_s3_etag would pick for this many parts; anything else the
+    // general kernel with 256-byte stages and the shortest step formulation.  Encoding a tensor map is
+    // host-side arithmetic into a struct on this stack: nothing is allocated.
     // per-part MD5s into the built-in array (one lane per part) ...
-    LaneArgs a{};
-    a.base = (const uint8_t *)d_data; a.base_bytes = size; a.stride = part_size;
-    a.table = (uint4 *)parts; a.n = np;
     const bool aligned = ((uintptr_t)d_data & 15) == 0 && (part_size & 15) == 0;
-    int rc = aligned ? enqueue_lanes<256, true, 4, 3, 4>(a, st) : enqueue_lanes<256, false, 4, 3, 4>(a, st);
+    const uint64_t n_full = size / part_size;               // whole parts; a ragged last part follows (or the one empty part)
+    int rc = 0;
+    uint64_t done_parts = 0;
+    if (aligned && n_full && part_size <= ((uint64_t)1 << 31) && tma_layout_ok(d_data, part_size, n_full)) {
+        CUtensorMap tmap, tail;
+        rc = encode_rows(&tmap, d_data, part_size, n_full, part_size);
+        if (rc) return rc;
+        const uint64_t tail_len = size - n_full * part_size;   // the ragged last part rides in the same launch
+        if (tail_len) {
+            rc = encode_rows(&tail, (const uint8_t *)d_data + n_full * part_size, tail_len, 1, (tail_len + 15) & ~(uint64_t)15);
+            if (rc) return rc;
+        }
+        rc = (n_full + 31) / 32 <= 148
+                 ? enqueue_chain<2, 2, 4, 2, 4, 4>(tmap, n_full, (uint32_t)part_size, (uint4 *)parts, st, 0, LANE_FINAL, &tail, (uint32_t)tail_len)
+                 : enqueue_chain<4, 1, 2, 4, 4, 4>(tmap, n_full, (uint32_t)part_size, (uint4 *)parts, st, 0, LANE_FINAL, &tail, (uint32_t)tail_len);
+        if (rc) return rc;
+        done_parts = np;
+    }
+    if (done_parts < np) {
+        LaneArgs a{};
+        a.base = (const uint8_t *)d_data + done_parts * part_size; a.base_bytes = size - done_parts * part_size; a.stride = part_size;
+        a.table = (uint4 *)parts + done_parts; a.n = np - done_parts;
+        rc = aligned ? enqueue_lanes<256, true, 4, 3, 4>(a, st) : enqueue_lanes<256, false, 4, 3, 4>(a, st);
+        if (rc) return rc;
+    }
+    // ... then the MD5 of those 16*np bytes, read back from the same array (one chain)
+    if (encode_tiled_fn() == nullptr) {
+        LaneArgs b{};
+        b.base = parts; b.base_bytes = np * 16; b.stride = np * 16;
+        b.table = (uint4 *)d_etag_md5_out; b.n = 1;
+        return enqueue_lanes<256, true, 4, 3, 4>(b, st);
+    }
+    CUtensorMap tmap2;
+    rc = encode_rows(&tmap2, parts, np * 16, 1, np * 16);
     if (rc) return rc;
-    // ... then the MD5 of those 16*np bytes, read back from the same array
-    LaneArgs b{};
-    b.base = parts; b.base_bytes = np * 16; b.stride = np * 16;
-    b.table = (uint4 *)d_etag_md5_out; b.n = 1;
-    return enqueue_lanes<256, true, 4, 3, 4>(b, st);
+    return enqueue_chain<2, 2, 4, 2, 4, 4>(tmap2, 1, (uint32_t)(np * 16), (uint4 *)d_etag_md5_out, st, 0, LANE_FINAL);
 }

@@ -290,9 +290,10 @@ TPIMD5_API int tpimd5_dev_synth_fill(tpimd5_ctx *ctx, int slot, void *d_out, uin
  *   - the array keeps the previous call's contents.  Nothing here needs it to start at zero: the
  *     second kernel reads exactly the 16 * nparts bytes the first kernel of the same call wrote.
  *   - the first call on each device (whichever thread makes it) looks up the array's device address
- *     and sets the shared-memory attributes of both kernel forms the call can launch (16-byte
- *     aligned input, and any other alignment); later calls on that device, from any thread, only
- *     enqueue.  Make that first call before any stream capture begins.
+ *     and sets the shared-memory attributes of every kernel form the call can launch (the two
+ *     TMA-fed shapes for 16-byte aligned data and part size, the general kernel for any other
+ *     alignment); later calls on that device, from any thread, only enqueue.  Make that first
+ *     call before any stream capture begins.
  *   - `device` is made current for the duration of the call and the thread's previous device is
  *     restored before returning, also on errors (as in every tpimd5_dev_* call). */
 #define TPIMD5_NOALLOC_MAX_PARTS 10000

@@ -263,7 +263,7 @@ def test_full_size_properties_config2():
 
 @pytest.mark.parametrize("variant", [0, 201, 202, 203, 204, 241, 244, 262, 245, 246, 247, 265,
                                      341, 342, 343, 344, 345, 346, 347, 348, 349, 301, 363,
-                                     441, 442, 443, 446, 448, 449, 461])
+                                     441, 442, 443, 446, 448, 449, 461, 365, 364, 262])
 def test_tensor_map_kernel_for_strided_units(variant):
     """Equal-sized units at a fixed stride through the TMA kernel: every stride class (multiples of
     16 around the 64/128-byte block and stage boundaries), unit counts that do not fill the last

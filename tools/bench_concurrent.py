@@ -38,7 +38,7 @@ def main():
         def run(i):
             got[i] = c.hash_buffers(*jobs[i])
         times = []
-        for rep in range(3):                              # the first round allocates staging buffers, tables and streams
+        for rep in range(5):                              # the first rounds allocate staging buffers, tables and streams
             th = [threading.Thread(target=run, args=(i,)) for i in range(k)]
             t0 = time.perf_counter()
             for t in th:
@@ -46,7 +46,7 @@ def main():
             for t in th:
                 t.join()
             times.append(time.perf_counter() - t0)
-        allk = min(times[1:])
+        allk = sorted(times[2:])[1]                       # median of the last three rounds
         ok = all(np.array_equal(g, w) for g, w in zip(got, want))
         t0 = time.perf_counter()
         for _ in range(3):
