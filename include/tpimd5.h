@@ -16,7 +16,8 @@
  *   - the caller owns every pointer it passes; nothing is retained after a call returns
  *     (cgo pointer rule).  The library owns staging memory, streams and device buffers.
  *   - there is NO CPU fallback: without a usable CUDA device tpimd5_init() fails.
- *   - a context may be used from many threads at once; calls that share a device queue up.
+ *   - a context may be used from many threads at once; calls that share a device overlap
+ *     (each leases staging buffers, a table and a stream; nothing is locked for a call's length).
  */
 #ifndef TPIMD5_H
 #define TPIMD5_H
@@ -48,7 +49,7 @@ typedef struct tpimd5_stream tpimd5_stream;
 /* ---- lifecycle ---------------------------------------------------------------------------
  * No counterpart in the reference (rclone needs no set-up to hash).  `device_ids` == NULL
  * means devices 0..n_devices-1.  `staging_bytes_per_device` sizes each of the pinned-host /
- * device staging buffers of the ingest pipeline (0 = default 256 MiB; up to eight per device,
+ * device staging buffers of the ingest pipeline (0 = default 256 MiB; up to twelve per device,
  * allocated on first use.  Ingest of large files is bounded by bytes in flight divided by the
  * time of the longest single MD5 chain, so callers that hash multi-GiB files do better with
  * 512 MiB: 32 instead of 23 GB/s on an 8 GiB file with 8 MiB parts). */
