@@ -27,6 +27,7 @@ The one JSON line carries, next to the C2 headline:
   c4         configs[3] scaled 1/64: Zipf sizes, whole-file MD5, byte-balanced LPT sharding
   c1         (N=1) configs[0]: 1,000 files / 1 GiB on tmpfs through machine.Transfer --checksum
   c2_files   (N=1) C2 from REAL files: 200,000 x 4 KiB files through tpimd5_hash_files
+  c3_file    (N=1) C3 from a REAL file: one 8 GiB checkpoint on tmpfs through tpimd5_s3_etag_file
 each with its own value, ms_per_step, roofline (for chain-starved workloads also the chain-latency
 bound resident_chains x 64 B x f_clk / 768 cycles) and, at N=1, a CPU figure beside it.
 `--impl reference` times the CPU path alone over the full C2 file set, all host threads, and
@@ -69,7 +70,7 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--only-c2", action="store_true", help="skip the c1/c3/c4/c5/c2_files sub-records")
     ap.add_argument("--sweep", action="store_true", help="print kernel-only GB/s for every kernel variant, then exit")
-    ap.add_argument("--workload", default="all", choices=["all", "c1", "c2", "c2_files", "c3", "c4", "c5"],
+    ap.add_argument("--workload", default="all", choices=["all", "c1", "c2", "c2_files", "c3", "c3_file", "c4", "c5"],
                     help="all = the driver's line (C2 headline + every sub-record); c2 = headline only; "
                          "any other = that sub-record alone, printed as its own line")
     return ap.parse_args()
@@ -731,6 +732,50 @@ def run_c2_files(env, n=200_000):
         shutil.rmtree(root, ignore_errors=True)
 
 
+def run_c3_file(env, size=(8 << 30) + 12345, part=8 << 20):
+    """C3 end to end for one checkpoint file: 8 GiB (+ a ragged last part) on tmpfs through tpimd5_s3_etag_file --
+    file reads into pinned staging, H2D, one lane per 8 MiB part, digest of digests, D2H -- against the CPU doing
+    the same from the file already in memory (one part per thread, all cores)."""
+    import shutil
+    import oracle
+    ctx = env.ctx
+    root = _tmp_root("tpi_c3f_")
+    path = os.path.join(root, "ckpt.bin")
+    try:
+        chunk = oracle.synth_files(3, 0, 1 << 20, 64, threads=os.cpu_count() or 1).tobytes()
+        with open(path, "wb") as f:
+            left = size
+            while left:
+                k = min(left, len(chunk))
+                f.write(chunk[:k])
+                left -= k
+        l0 = ctx.launch_count()
+        etag, n, parts = ctx.s3_etag_file(path, size, part)            # warm: staging buffers
+        t = []
+        for _ in range(3):
+            t0 = time.perf_counter()
+            etag, n, parts = ctx.s3_etag_file(path, size, part)
+            t.append(time.perf_counter() - t0)
+        launches = int(ctx.launch_count() - l0)
+        buf = np.fromfile(path, dtype=np.uint8)
+        eng, kind = cpu_engine()
+        threads = os.cpu_count() or 1
+        t0 = time.perf_counter()
+        o_etag, o_n, o_parts = oracle.s3_etag(buf, part, threads=threads, engine=eng)
+        tc = time.perf_counter() - t0
+        if (etag, n) != (o_etag, o_n) or not np.array_equal(parts, o_parts):
+            raise SystemExit("bench.py: c3_file ETag differs from the CPU path's")
+        mean = sum(t) / 3
+        return {"workload": f"C3 from a real file: one {size / 2**30:.1f} GiB checkpoint on tmpfs, S3 multipart ETag with 8 MiB parts "
+                            f"({n} parts, the last one ragged), tpimd5_s3_etag_file (reads + H2D + kernels + D2H)",
+                "value": round(size / mean / 1e9, 3), "unit": "GB/s", "steps": 3, "warmup": 1, "ms_per_step": round(1e3 * mean, 1),
+                "best_ms": round(1e3 * min(t), 1), "etag": env.tpi.s3_etag_text(etag, n), "gpu_launches": launches,
+                "cpu_baseline": {"value": round(size / tc / 1e9, 3), "unit": "GB/s", "cores": threads, "kind": "port",
+                                 "sample": f"the same file already read into memory, {kind}, one part per task on {threads} threads, one pass"}}
+    finally:
+        shutil.rmtree(root, ignore_errors=True)
+
+
 def run_sweep(env):
     args, torch, ctx, dev = env.args, env.torch, env.ctx, env.dev
     n, flen = args.files, FILE_BYTES
@@ -775,7 +820,7 @@ def main():
     env = Env(args, torch, dist, tpi, ctx, dev, rank, local_rank, world)
     env.near = near
 
-    sections = {"c1": run_c1, "c2_files": run_c2_files, "c3": run_c3, "c4": run_c4, "c5": run_c5}
+    sections = {"c1": run_c1, "c2_files": run_c2_files, "c3": run_c3, "c3_file": run_c3_file, "c4": run_c4, "c5": run_c5}
     if args.sweep:
         run_sweep(env)
     elif args.workload in sections:
@@ -795,6 +840,7 @@ def main():
             if world == 1:
                 subs["c1"] = run_c1(env)
                 subs["c2_files"] = run_c2_files(env)
+                subs["c3_file"] = run_c3_file(env)
             line.update(subs)
         if rank == 0:
             print(json.dumps(line), flush=True)
