@@ -83,3 +83,33 @@ def test_digest_string_forms():
         assert tpi.md5_from_etag(d.hex()[:-1] + 'g') is None and tpi.md5_from_etag('') is None
         assert tpi.md5_from_etag(d.hex() + "-3") is None and tpi.md5_from_etag(d.hex()[:-1]) is None
         assert tpi.s3_etag_text(d, 8192) == d.hex() + "-8192"
+
+
+def test_s3_plan_decision_matches_the_restated_rule():
+    """tpimd5_s3_plan_parts is pure host arithmetic (no GPU): single PutObject below the cutoff, multipart at and
+    above it, part size by rclone's growth rule -- against the oracle's restatement, defaults included."""
+    import oracle
+    cases = [(0, 0, 0, 0), (1, 0, 0, 0), ((200 << 20) - 1, 0, 0, 0), (200 << 20, 0, 0, 0), (64 << 30, 0, 0, 0), (64 << 30, 8 << 20, 0, 0),
+             (5 << 40, 0, 0, 0), (1000, 64, 1, 10), (1000, 64, 1001, 10), (10000 * (5 << 20), 0, 0, 0), (10000 * (5 << 20) - 1, 0, 0, 0)]
+    for size, chunk, cutoff, maxp in cases:
+        multi, part, n = tpi.s3_plan_parts(size, chunk, cutoff, maxp)
+        c, k, m = chunk or (5 << 20), cutoff or (200 << 20), maxp or 10000
+        if size >= k:
+            want_part = oracle.s3_part_size(size, c, m)
+            assert (multi, part, n) == (True, want_part, oracle.s3_nparts(size, want_part)), (size, chunk, cutoff, maxp)
+            assert n <= m or size // c < m
+        else:
+            assert (multi, part, n) == (False, size, 1)
+
+
+def test_etag_rule_agrees_with_the_oracle():
+    import hashlib
+    import oracle
+    d = hashlib.md5(b"x").hexdigest()
+    for etag in (d, d.upper(), '"' + d + '"', '"' + d.upper() + '"', d + "-2", d[:-1], d[:-1] + "g", "", '""', '"' + d, d + '"'):
+        assert tpi.md5_from_etag(etag) == oracle.md5_from_etag(etag), etag
+
+
+def test_pathlist_keeps_its_strings_alive():
+    pl = tpi.PathList(["/tmp/a", "/tmp/b/c"])
+    assert len(pl) == 2 and pl.array[1] == b"/tmp/b/c"
