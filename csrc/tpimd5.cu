@@ -869,7 +869,8 @@ static int launch_lanes(tpimd5_ctx *ctx, const LaneArgs &a0, bool aligned, cudaS
     // ragged latency kernel (md5_ragged_chain.cuh).  It needs per-unit offset/length arrays and 16-byte aligned
     // units, which is what the host pipeline's packer produces.  Variant 500 + x forces it for tests.
     const uint64_t warps = (a.n + 31) / 32;
-    if ((ctx->variant.load() == 0 || loader == 5) && aligned && a.off && a.len && warps <= (uint64_t)148 * 12) {
+    if ((ctx->variant.load() == 0 || loader == 5) && aligned && a.off && a.len && warps <= (uint64_t)148 * 12 &&
+        a.base_bytes < ((uint64_t)1 << 32)) {      // (the kernel keeps a unit's length in 32 bits: one staging buffer's worth)
         int rc;
         if (loader == 5 && shape == 2) rc = launch_ragged_chain_cfg<4, 3, 2, 256, 4>(a, st);
         else if (loader == 5 && shape == 3) rc = launch_ragged_chain_cfg<4, 3, 2, 256, 6>(a, st);
