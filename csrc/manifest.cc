@@ -653,6 +653,7 @@ extern "C" int tpimd5_plan_transfer(tpimd5_ctx *ctx, const tpimd5_manifest *src,
 // comparison mode needs (as rclone does lazily), decide per object with equal(), create the
 // directories, copy, carry the modification time over, then verify each copy by digest.
 #include <fcntl.h>
+#include <atomic>
 #include <sys/sendfile.h>
 #include <unistd.h>
 
@@ -786,12 +787,39 @@ extern "C" int tpimd5_transfer_local(tpimd5_ctx *ctx, const char *source, const 
         }
         const size_t slash = to.rfind('/');
         if (slash != std::string::npos) { rc = mkdir_p(to.substr(0, slash)); if (rc) return rc; }
-        uint64_t nbytes = 0;
-        rc = copy_file(src + "/" + e.path, to, e.mtime_ns, &nbytes);
-        if (rc) return rc;
-        ++st.transferred;
-        st.bytes_transferred += nbytes;
         moved.push_back(k);
+    }
+    // the copies themselves, several at a time (rclone: --transfers, 4 by default; local copies are cheap: 8)
+    if (!moved.empty()) {
+        std::atomic<size_t> next{0};
+        std::atomic<uint64_t> copied{0};
+        std::mutex err_mu;
+        int first_rc = 0;
+        std::string first_err;
+        auto worker = [&] {
+            for (;;) {
+                const size_t i = next.fetch_add(1);
+                if (i >= moved.size()) break;
+                const Entry &e = ms.e[moved[i]];
+                uint64_t nbytes = 0;
+                const int r = copy_file(src + "/" + e.path, dst + "/" + e.path, e.mtime_ns, &nbytes);
+                if (r) {
+                    std::lock_guard<std::mutex> g(err_mu);
+                    if (!first_rc) { first_rc = r; first_err = tpimd5_last_error(); }
+                    next.store(moved.size());               // stop handing out work
+                    break;
+                }
+                copied.fetch_add(nbytes);
+            }
+        };
+        std::vector<std::thread> th;
+        const size_t nth = std::min<size_t>(8, moved.size());
+        for (size_t t = 1; t < nth; ++t) th.emplace_back(worker);
+        worker();
+        for (auto &t : th) t.join();
+        if (first_rc) return fail(first_rc, first_err);
+        st.transferred += moved.size();
+        st.bytes_transferred += copied.load();
     }
     // post-transfer check (rclone: size, then the common hash): source and copy hashed in one GPU pass
     if (!moved.empty()) {
