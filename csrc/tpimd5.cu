@@ -1607,6 +1607,10 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
         if (rc) return rc;
         CU(cudaEventRecord(s.ev_done[bi], sk));
         for (size_t i = 0; i < np; ++i) batch_bytes += pieces[i].len;
+        if (trace_on())
+            fprintf(stderr, "[tpimd5]   batch %d: %zu units, %.1f MiB, longest %.2f MiB, launched at %.1f ms%s\n", batch, np,
+                    batch_bytes / 1048576.0, np ? pieces[order.empty() ? 0 : order[0]].len / 1048576.0 : 0.0, 1e3 * (trace_now() - tr0),
+                    uniform ? " (uniform)" : "");
         ctx->bytes_staged.fetch_add(batch_bytes);
         total_bytes += batch_bytes;
         batch_bytes = 0;
