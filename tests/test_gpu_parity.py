@@ -405,6 +405,68 @@ def test_one_context_many_threads(ctx):
     assert not errs, errs
 
 
+def test_mixed_calls_from_many_threads_and_an_error_in_one_of_them(ctx, tmp_path):
+    """Twelve threads on one context, every kind of host call at once -- buffers, files, S3 ETags, streams, diffs --
+    while one thread keeps asking for a file that has shrunk since its listing.  That call must fail with TPIMD5_EIO every
+    time, hand back everything it leased, and leave the other threads' results bit-exact."""
+    import threading
+    rng = np.random.default_rng(72)
+    lengths = [int(x) for x in rng.integers(0, 200000, 120)] + [3 << 20, (5 << 20) + 7]
+    buf, off, ln = oracle.synth_packed(72, lengths, align=16)
+    want = oracle.md5_batch(buf, off, ln, threads=4)
+    paths = []
+    for i in range(40):
+        p = tmp_path / f"f{i:02d}.bin"
+        buf[int(off[i]): int(off[i] + ln[i])].tofile(p)
+        paths.append(str(p))
+    short = tmp_path / "shrunk.bin"
+    short.write_bytes(b"x" * 100)
+    big = buf[int(off[-1]): int(off[-1] + ln[-1])]
+    etag_want = oracle.s3_etag(big, 1 << 20)
+    errs, eio = [], []
+
+    def worker(k):
+        try:
+            for it in range(4):
+                kind = (k + it) % 6
+                if kind == 0:
+                    sel = np.arange(k % 5, len(lengths), 5)
+                    assert np.array_equal(ctx.hash_buffers(buf, off[sel], ln[sel]), want[sel])
+                elif kind == 1:
+                    assert np.array_equal(ctx.hash_files(paths, ln[:40]), want[:40])
+                elif kind == 2:
+                    e, n, parts = ctx.s3_etag_buffer(big, 1 << 20)
+                    assert (e, n) == etag_want[:2] and np.array_equal(parts, etag_want[2])
+                elif kind == 3:
+                    h = ctx.stream()
+                    for lo in range(0, int(ln[-2]), 700001):
+                        h.write(buf[int(off[-2]) + lo: int(off[-2]) + min(int(ln[-2]), lo + 700001)])
+                    assert h.sum() == want[-2].tobytes()
+                    h.close()
+                elif kind == 4:
+                    other = want.copy()
+                    other[[5, 77], 3] ^= 1
+                    assert ctx.diff(want, other).tolist() == [5, 77]
+                else:
+                    try:
+                        ctx.hash_files(paths[:10] + [str(short)], list(ln[:10]) + [5000])
+                        errs.append("a shrunk file produced digests")
+                    except tpi.TpiMd5Error as e:
+                        assert e.code == -4 and e.failed_index == 10, (e.code, e.failed_index)
+                        eio.append(1)
+        except Exception as e:      # noqa: BLE001
+            errs.append(repr(e))
+
+    th = [threading.Thread(target=worker, args=(k,)) for k in range(12)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errs, errs
+    assert len(eio) == 8                                           # 12 threads x 4 rounds, one kind in six
+    p = ctx.progress()
+    assert p["calls_started"] == p["calls_finished"]
+    assert np.array_equal(ctx.hash_buffers(buf, off, ln), want)    # and the context is as good as new
+
+
 def test_concurrent_callers_overlap_on_one_gpu():
     """Eight threads, one context, one GPU, each hashing its own workdir whose longest file is 8 MiB (one job is
     bound by that file's serial chain and leaves the GPU almost idle): the calls lease staging buffers, tables
