@@ -108,9 +108,14 @@ md5_chain_tma_kernel(const __grid_constant__ CUtensorMap tmap_main, uint64_t n_m
                 if (k >= (uint32_t)NSTAGE) mbar_wait(empty, ((k / NSTAGE) - 1u) & 1u);   // the warp has read this buffer's previous stage
                 mbar_expect_tx(full, Cfg::STAGE_BYTES);
                 const uint32_t dst = sbase + w * Cfg::WARP_BYTES + buf * Cfg::STAGE_BYTES;
+                if (TILES > 1 && (flags & LANE_BOX3D) && !is_tail) {
+                    // unit_len is a multiple of 128: the buffer seen as (byte in chunk, unit, chunk) -- one request per stage
+                    tma_load_3d(dst, tmap, 0u, (uint32_t)(cta_u0 + w * 32u), k * TILES, full);
+                } else {
 #pragma unroll
-                for (int t = 0; t < TILES; ++t)                // a box wholly past unit_len (or past n) arrives as zeros
-                    tma_load_2d(dst + t * Cfg::TILE_BYTES, tmap, (k * TILES + t) << 7, (uint32_t)(cta_u0 + w * 32u), full);
+                    for (int t = 0; t < TILES; ++t)            // a box wholly past unit_len (or past n) arrives as zeros
+                        tma_load_2d(dst + t * Cfg::TILE_BYTES, tmap, (k * TILES + t) << 7, (uint32_t)(cta_u0 + w * 32u), full);
+                }
             }
         }
         return;

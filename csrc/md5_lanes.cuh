@@ -23,6 +23,7 @@ namespace tpimd5 {
 
 constexpr uint32_t LANE_FINAL = 1u;  // pad and finalise: table[out] receives the digest
 constexpr uint32_t LANE_CONT = 2u;   // start from the chaining value in table[out] instead of the IV
+constexpr uint32_t LANE_BOX3D = 4u;  // (strided TMA kernels) the main tensor map is the 3-D view: one request per stage
 
 struct LaneArgs {
     const uint8_t *base;       // device buffer holding every unit of this launch

@@ -30,6 +30,15 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *tma
         : "memory");
 }
 
+// The same for a 3-D view of the buffer -- (byte within a 128-byte chunk, unit, chunk index) -- whose box is 128 bytes x
+// 32 units x TILES chunks: ONE request fetches a whole stage, landing as TILES consecutive swizzled tiles.
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *tmap, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t mbar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
+        "l"(tmap), "r"(c0), "r"(c1), "r"(c2), "r"(mbar)
+        : "memory");
+}
+
 // TILES: boxes per stage.  1 keeps shared memory small (20 warps/SM for throughput-bound launches);
 // 2 or 4 halve / quarter the per-stage costs that sit on a lone chain's critical path (mbarrier wait,
 // TMA issue, loop) for launches with too few chains to fill the SMs (S3 parts, large files).

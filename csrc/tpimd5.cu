@@ -764,13 +764,22 @@ static int launch_chain(const CUtensorMap &tmap, uint64_t n, uint32_t unit_len, 
 static bool chain_launch_fits(uint64_t n) { return (n + 31) / 32 <= (uint64_t)148 * 12; }
 
 // The latency kernel in the shape that suits the launch's warp count (see launch_strided_tma).
+struct RowsDesc;
+static bool encode_rows3(CUtensorMap *tmap, const RowsDesc &d, uint32_t tiles);
+
 static int launch_chain_default(const CUtensorMap &tmap, uint64_t n, uint32_t ul, uint4 *table, cudaStream_t st, uint64_t prior,
-                                uint32_t flags, const CUtensorMap *tail = nullptr, uint32_t tail_len = 0) {
+                                uint32_t flags, const CUtensorMap *tail = nullptr, uint32_t tail_len = 0, const RowsDesc *rows = nullptr) {
     const uint64_t warps = (n + 31) / 32;
-    if (warps <= 148) return launch_chain_cfg<2, 2, 4, 2, 4, 4>(tmap, n, ul, table, st, prior, flags, tail, tail_len);
-    if (warps <= 592) return launch_chain_cfg<4, 1, 2, 4, 4, 4>(tmap, n, ul, table, st, prior, flags, tail, tail_len);
-    if (warps <= 888) return launch_chain_cfg<3, 1, 2, 4, 4, 4>(tmap, n, ul, table, st, prior, flags, tail, tail_len);
-    if (warps <= (uint64_t)148 * 12) return launch_chain_cfg<4, 3, 2, 2, 6, 4>(tmap, n, ul, table, st, prior, flags, tail, tail_len);
+    CUtensorMap t3;
+    // latency shapes with several boxes per stage: one 3-D request per stage where the rows allow it
+    const uint32_t tiles = warps <= 148 ? 2 : warps <= 888 ? 4 : 2;
+    const bool box3d = warps <= (uint64_t)148 * 12 && rows && encode_rows3(&t3, *rows, tiles);
+    const CUtensorMap &tm = box3d ? t3 : tmap;
+    if (box3d) flags |= LANE_BOX3D;
+    if (warps <= 148) return launch_chain_cfg<2, 2, 4, 2, 4, 4>(tm, n, ul, table, st, prior, flags, tail, tail_len);
+    if (warps <= 592) return launch_chain_cfg<4, 1, 2, 4, 4, 4>(tm, n, ul, table, st, prior, flags, tail, tail_len);
+    if (warps <= 888) return launch_chain_cfg<3, 1, 2, 4, 4, 4>(tm, n, ul, table, st, prior, flags, tail, tail_len);
+    if (warps <= (uint64_t)148 * 12) return launch_chain_cfg<4, 3, 2, 2, 6, 4>(tm, n, ul, table, st, prior, flags, tail, tail_len);
     // enough chains to fill the SMs: the integer pipes are the limit -- 4 hashing warps + the producer per CTA, six
     // CTAs per SM (24 hashing warps), one box per stage, step mode 6 (the additions spread over both integer pipes)
     return launch_chain_cfg<4, 6, 2, 1, 6, 2>(tmap, n, ul, table, st, prior, flags, tail, tail_len);
@@ -788,6 +797,24 @@ static int encode_rows(CUtensorMap *tmap, const void *base, uint64_t row_bytes, 
     return 0;
 }
 
+// The 3-D view of the same rows for the latency shapes: (byte within a 128-byte chunk, row, chunk), box 128 x 32 x
+// `tiles`, so that a stage of `tiles` boxes is ONE TMA request.  Only when a row is a whole number of chunks (the view
+// would otherwise reach up to 127 bytes past the last row's end).
+struct RowsDesc {
+    const void *base;
+    uint64_t row_bytes, rows, pitch;
+};
+static bool encode_rows3(CUtensorMap *tmap, const RowsDesc &d, uint32_t tiles) {
+    if (tiles < 2 || d.row_bytes % 128 != 0 || d.row_bytes == 0 || encode_tiled_fn() == nullptr) return false;
+    const cuuint64_t gdim[3] = {128, d.rows, d.row_bytes / 128};
+    const cuuint64_t gstride[2] = {d.pitch, 128};
+    const cuuint32_t box[3] = {128, 32, tiles};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    return encode_tiled_fn()(tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void *>(d.base), gdim, gstride, box, estr,
+                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 // Units too long for one tensor-map row (large files: C4's 32 GiB object): CHAIN_SEG bytes of every unit
 // per launch, the chaining values carried from launch to launch in the digest table.
 static int launch_long_units(tpimd5_ctx *ctx, const void *base, uint64_t stride, uint64_t unit_len, uint64_t n, uint4 *table,
@@ -798,7 +825,8 @@ static int launch_long_units(tpimd5_ctx *ctx, const void *base, uint64_t stride,
         int rc = encode_rows(&tmap, (const uint8_t *)base + done, seg, n, stride);
         if (rc) return rc;
         const uint32_t flags = (done ? LANE_CONT : 0u) | (done + seg == unit_len ? LANE_FINAL : 0u);
-        rc = launch_chain_default(tmap, n, (uint32_t)seg, table, st, done, flags);
+        const RowsDesc rows{(const uint8_t *)base + done, seg, n, stride};
+        rc = launch_chain_default(tmap, n, (uint32_t)seg, table, st, done, flags, nullptr, 0, &rows);
         if (rc) return rc;
         ctx->launches.fetch_add(1);
     }
@@ -815,8 +843,9 @@ static int launch_strided_tma(tpimd5_ctx *ctx, const void *base, uint64_t stride
     if (tail_len)
         if (int rc0 = encode_rows(&tail, (const uint8_t *)base + n * stride, tail_len, 1, (tail_len + 15) & ~(uint64_t)15)) return rc0;
     int rc;
+    const RowsDesc rows{base, unit_len, n, stride};
     if (tail_len) {
-        rc = launch_chain_default(tmap, n, (uint32_t)unit_len, table, st, 0, LANE_FINAL, &tail, (uint32_t)tail_len);
+        rc = launch_chain_default(tmap, n, (uint32_t)unit_len, table, st, 0, LANE_FINAL, &tail, (uint32_t)tail_len, &rows);
         if (rc == 0) ctx->launches.fetch_add(1);
         return rc;
     }
@@ -840,7 +869,7 @@ static int launch_strided_tma(tpimd5_ctx *ctx, const void *base, uint64_t stride
     // All with four blocks per loop iteration.
     // Beyond that the same kernel in its throughput shape (see launch_chain_default).
     if (shape == 0) {
-        rc = launch_chain_default(tmap, n, (uint32_t)unit_len, table, st, 0, LANE_FINAL);
+        rc = launch_chain_default(tmap, n, (uint32_t)unit_len, table, st, 0, LANE_FINAL, nullptr, 0, &rows);
         if (rc == 0) ctx->launches.fetch_add(1);
         return rc;
     }
