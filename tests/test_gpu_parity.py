@@ -467,6 +467,36 @@ def test_mixed_calls_from_many_threads_and_an_error_in_one_of_them(ctx, tmp_path
     assert np.array_equal(ctx.hash_buffers(buf, off, ln), want)    # and the context is as good as new
 
 
+@pytest.mark.parametrize("variant", [0, 501, 502, 503])
+def test_ragged_latency_kernel_shapes(variant):
+    """Ragged host batches through md5_ragged_chain_kernel in each of its shapes (512-byte stages; 256-byte stages in step
+    modes 4 and 6, which the library picks from 593 and 889 warps of units): every length class -- empty, sub-block,
+    55/56/63/64 bytes mod 64, stage multiples +- 1, lengths that end in every block of an iteration -- sorted and
+    unsorted, plus units longer than a staging buffer (chained across launches) and a batch of more than 592 warps."""
+    rng = np.random.default_rng(90 + variant)
+    lengths = list(range(0, 200)) + [256 * k + d for k in range(1, 40) for d in (-1, 0, 1, 55, 56, 63)]
+    lengths += [int(x) for x in rng.integers(0, 300000, 600)] + [(9 << 20) + 5, 5 << 20, 0, 0]
+    rng.shuffle(lengths)
+    buf, off, ln = oracle.synth_packed(73, lengths, align=1)
+    want = oracle.md5_batch(buf, off, ln, threads=8)
+    with tpi.Context([0], staging_bytes=8 << 20) as c:
+        if variant:
+            c.set_variant(variant)
+        got = c.hash_buffers(buf, off, ln)
+        bad = np.nonzero((got != want).any(axis=1))[0]
+        assert bad.size == 0, (variant, bad[:5], ln[bad[:5]])
+    # many small ragged units in one batch: more than 592 warps of them
+    lengths = [int(x) for x in rng.integers(0, 3000, 24000)]
+    buf, off, ln = oracle.synth_packed(74, lengths, align=1)
+    want = oracle.md5_batch(buf, off, ln, threads=8)
+    with tpi.Context([0]) as c:
+        if variant:
+            c.set_variant(variant)
+        got = c.hash_buffers(buf, off, ln)
+        bad = np.nonzero((got != want).any(axis=1))[0]
+        assert bad.size == 0, (variant, bad[:5], ln[bad[:5]])
+
+
 def test_concurrent_callers_overlap_on_one_gpu():
     """Eight threads, one context, one GPU, each hashing its own workdir whose longest file is 8 MiB (one job is
     bound by that file's serial chain and leaves the GPU almost idle): the calls lease staging buffers, tables
