@@ -1438,12 +1438,25 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
         if (!pinned && !(force && force[0] == '1')) direct = false;
     }
     if (direct) {
-        uint64_t bytes = 0;
-        for (size_t i = 0; i < nu && direct; ++i) {
-            const uint32_t u = units[i];
-            if (i && job.off[u] < job.off[units[i - 1]] + job.len[units[i - 1]]) direct = false;
-            bytes += job.len[u];
-        }
+        // (millions of units: checked by the pool, 64 Ki units per item)
+        constexpr size_t CHUNK = 1u << 16;
+        std::atomic<uint64_t> a_bytes{0};
+        std::atomic<bool> in_order{true};
+        std::function<void(size_t)> check = [&](size_t c) {
+            uint64_t t = 0;
+            bool ok = true;
+            const size_t hi = std::min(nu, (c + 1) * CHUNK);
+            for (size_t i = c * CHUNK; i < hi; ++i) {
+                const uint32_t u = units[i];
+                if (i && job.off[u] < job.off[units[i - 1]] + job.len[units[i - 1]]) ok = false;
+                t += job.len[u];
+            }
+            a_bytes.fetch_add(t);
+            if (!ok) in_order.store(false);
+        };
+        ctx->pool->parallel_for((nu + CHUNK - 1) / CHUNK, 1, check);
+        const uint64_t bytes = a_bytes.load();
+        direct = in_order.load();
         if (direct) {
             const uint64_t span = job.off[units[nu - 1]] + job.len[units[nu - 1]] - job.off[units[0]];
             if (span > bytes + bytes / 4 + (1u << 20)) direct = false;
@@ -1713,12 +1726,24 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
     if (trace_on())
         fprintf(stderr, "[tpimd5] device %d: %zu units, %d batches, total %.1f ms: plan %.1f, buffer wait %.1f, fill %.1f, final sync %.1f\n",
                 s.dev, nu, batch, 1e3 * (trace_now() - tr0), 1e3 * tr_plan, 1e3 * tr_wait, 1e3 * tr_fill, 1e3 * (trace_now() - tr_s0));
-    // table row i belongs to unit units[i]; runs of consecutive units move as one copy
-    for (size_t i = 0; i < nu;) {
-        size_t j = i + 1;
-        while (j < nu && units[j] == units[j - 1] + 1) ++j;
-        memcpy(job.out + 16 * (size_t)units[i], h_table + 16 * i, 16 * (j - i));
-        i = j;
+    // table row i belongs to unit units[i]; runs of consecutive units move as one copy (16 MB of digests for a
+    // million files: the pool moves them, 64 Ki rows per item)
+    {
+        constexpr size_t CHUNK = 1u << 16;
+        std::function<void(size_t)> home = [&](size_t c) {
+            const size_t hi = std::min(nu, (c + 1) * CHUNK);
+            if (!units.idx) {
+                memcpy(job.out + 16 * ((size_t)units.base + c * CHUNK), h_table + 16 * c * CHUNK, 16 * (hi - c * CHUNK));
+                return;
+            }
+            for (size_t i = c * CHUNK; i < hi;) {
+                size_t j = i + 1;
+                while (j < hi && units[j] == units[j - 1] + 1) ++j;
+                memcpy(job.out + 16 * (size_t)units[i], h_table + 16 * i, 16 * (j - i));
+                i = j;
+            }
+        };
+        ctx->pool->parallel_for((nu + CHUNK - 1) / CHUNK, 1, home);
     }
     ctx->units_done.fetch_add(nu);
     ctx->bytes_done.fetch_add(total_bytes);
@@ -1821,6 +1846,33 @@ extern "C" int tpimd5_hash_buffers(tpimd5_ctx *ctx, const uint8_t *base, const u
     Job job;
     job.n = n; job.base = base; job.off = offsets; job.len = lengths; job.out = digests_out;
     return run_job(ctx, job);
+}
+
+extern "C" int tpimd5_units_extent(tpimd5_ctx *ctx, const uint64_t *offsets, const uint64_t *lengths, size_t n, uint64_t *extent_out) {
+    if (!ctx || !extent_out) return fail(TPIMD5_EINVAL, "units_extent: null pointer");
+    *extent_out = 0;
+    if (n == 0) return 0;
+    if (!offsets || !lengths) return fail(TPIMD5_EINVAL, "units_extent: null pointer");
+    constexpr size_t CHUNK = 1u << 16;
+    std::atomic<uint64_t> a_end{0};
+    std::atomic<bool> wrapped{false};
+    std::function<void(size_t)> scan = [&](size_t c) {
+        uint64_t e = 0;
+        bool w = false;
+        const size_t hi = std::min(n, (c + 1) * CHUNK);
+        for (size_t i = c * CHUNK; i < hi; ++i) {
+            const uint64_t end = offsets[i] + lengths[i];
+            w |= end < offsets[i];
+            e = std::max(e, end);
+        }
+        if (w) wrapped.store(true);
+        uint64_t cur = a_end.load();
+        while (e > cur && !a_end.compare_exchange_weak(cur, e)) {}
+    };
+    ctx->pool->parallel_for((n + CHUNK - 1) / CHUNK, 1, scan);
+    if (wrapped.load()) return fail(TPIMD5_ERANGE, "units_extent: an offset + length overflows 64 bits");
+    *extent_out = a_end.load();
+    return 0;
 }
 
 extern "C" int tpimd5_hash_files(tpimd5_ctx *ctx, const char *const *paths, const uint64_t *sizes, size_t n,

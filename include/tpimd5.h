@@ -82,6 +82,11 @@ TPIMD5_API int tpimd5_hash_buffers(tpimd5_ctx *ctx, const uint8_t *base, const u
                         size_t n, uint8_t *digests_out);
 TPIMD5_API int tpimd5_hash_files(tpimd5_ctx *ctx, const char *const *paths, const uint64_t *sizes, size_t n,
                       uint8_t *digests_out, size_t *failed_index_out);
+/* Helper for bindings (no reference counterpart): the end of the furthest unit, max over i of offsets[i] +
+ * lengths[i] (0 for n == 0), computed on the context's worker pool -- what a cgo / ctypes wrapper compares with the
+ * length of the slice it was handed before it passes `base` to tpimd5_hash_buffers, which cannot know it.
+ * TPIMD5_ERANGE if an offset + length overflows 64 bits. */
+TPIMD5_API int tpimd5_units_extent(tpimd5_ctx *ctx, const uint64_t *offsets, const uint64_t *lengths, size_t n, uint64_t *extent_out);
 
 /* ---- S3 multipart ------------------------------------------------------------------------
  * Replaces [rclone] backend/s3 uploadMultipart's per-chunk md5.Sum(buf) and the final

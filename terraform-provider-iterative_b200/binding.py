@@ -19,7 +19,7 @@ _lib: Optional[C.CDLL] = None
 EXPORTS = [
     "tpimd5_device_count", "tpimd5_init", "tpimd5_destroy", "tpimd5_ctx_devices", "tpimd5_get_progress", "tpimd5_last_error",
     "tpimd5_version", "tpimd5_hash_buffers", "tpimd5_hash_files", "tpimd5_s3_part_size", "tpimd5_s3_nparts",
-    "tpimd5_s3_etag_buffer", "tpimd5_s3_etag_file", "tpimd5_s3_plan_parts", "tpimd5_s3_upload_plan", "tpimd5_stream_open", "tpimd5_stream_write",
+    "tpimd5_s3_etag_buffer", "tpimd5_s3_etag_file", "tpimd5_s3_plan_parts", "tpimd5_units_extent", "tpimd5_s3_upload_plan", "tpimd5_stream_open", "tpimd5_stream_write",
     "tpimd5_stream_write_many", "tpimd5_stream_sum", "tpimd5_stream_reset", "tpimd5_stream_close", "tpimd5_diff",
     "tpimd5_dev_hash_buffers", "tpimd5_dev_s3_etag", "tpimd5_dev_diff", "tpimd5_dev_synth_fill",
     "tpimd5_dev_s3_etag_noalloc", "tpimd5_filter_new", "tpimd5_filter_free", "tpimd5_filter_include", "tpimd5_filter_include_dir",
@@ -67,6 +67,7 @@ def load_library() -> C.CDLL:
         "tpimd5_s3_etag_buffer": (i32, [vp, vp, u64, u64, vp, vp, C.POINTER(u32)]),
         "tpimd5_s3_etag_file": (i32, [vp, C.c_char_p, u64, u64, vp, vp, C.POINTER(u32)]),
         "tpimd5_s3_plan_parts": (u32, [u64, u64, u64, u32, C.POINTER(i32), C.POINTER(u64)]),
+        "tpimd5_units_extent": (C.c_int, [vp, vp, vp, C.c_size_t, C.POINTER(u64)]),
         "tpimd5_s3_upload_plan": (i32, [vp, C.c_char_p, u64, u64, u64, u32, u32, vp, vp, vp]),
         "tpimd5_stream_open": (i32, [vp, C.POINTER(vp)]),
         "tpimd5_stream_write": (i32, [vp, vp, sz]),
@@ -271,7 +272,9 @@ class Context:
             bp = base
         else:
             a = _u8(base)
-            if off.size and int((off + ln).max()) > a.size:
+            end = C.c_uint64()
+            _check(self._L.tpimd5_units_extent(self._h, off.ctypes.data, ln.ctypes.data, off.size, C.byref(end)))
+            if end.value > a.size:
                 raise ValueError("a unit runs past the end of the buffer")
             bp = a.ctypes.data
         _check(self._L.tpimd5_hash_buffers(self._h, bp, off.ctypes.data, ln.ctypes.data, off.size, out.ctypes.data))

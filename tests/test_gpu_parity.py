@@ -467,6 +467,30 @@ def test_mixed_calls_from_many_threads_and_an_error_in_one_of_them(ctx, tmp_path
     assert np.array_equal(ctx.hash_buffers(buf, off, ln), want)    # and the context is as good as new
 
 
+def test_units_extent_and_the_binding_bounds_check():
+    """tpimd5_units_extent (the helper a binding checks its slice length with): the furthest unit end, over more
+    units than one pool item, overflow refused; the Python binding refuses a unit past the end of its buffer."""
+    import ctypes as C
+    rng = np.random.default_rng(12)
+    n = 300000
+    off = rng.integers(0, 1 << 40, n).astype(np.uint64)
+    ln = rng.integers(0, 1 << 30, n).astype(np.uint64)
+    with tpi.Context([0]) as c:
+        end = C.c_uint64(7)
+        L = tpi.load_library()
+        assert L.tpimd5_units_extent(c._h, off.ctypes.data, ln.ctypes.data, n, C.byref(end)) == 0
+        assert end.value == int((off + ln).max())
+        assert L.tpimd5_units_extent(c._h, off.ctypes.data, ln.ctypes.data, 0, C.byref(end)) == 0 and end.value == 0
+        off[123456] = np.uint64(2**64 - 5)
+        ln[123456] = np.uint64(10)
+        assert L.tpimd5_units_extent(c._h, off.ctypes.data, ln.ctypes.data, n, C.byref(end)) == -6   # TPIMD5_ERANGE
+        buf = np.zeros(1000, dtype=np.uint8)
+        with pytest.raises(ValueError):
+            c.hash_buffers(buf, np.array([0, 990], dtype=np.uint64), np.array([10, 11], dtype=np.uint64))
+        got = c.hash_buffers(buf, np.array([0, 990], dtype=np.uint64), np.array([10, 10], dtype=np.uint64))
+        assert np.array_equal(got, oracle.md5_batch(buf, np.array([0, 990]), np.array([10, 10])))
+
+
 @pytest.mark.parametrize("variant", [0, 501, 502, 503])
 def test_ragged_latency_kernel_shapes(variant):
     """Ragged host batches through md5_ragged_chain_kernel in each of its shapes (512-byte stages; 256-byte stages in step
