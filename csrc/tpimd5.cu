@@ -361,6 +361,10 @@ struct Slot {
     uint8_t *h_stage[NBUF] = {}, *d_stage[NBUF] = {};
     uint8_t *h_desc_raw[NBUF] = {}, *d_desc_raw[NBUF] = {};
     cudaEvent_t ev_done[NBUF] = {};
+    // a batch that carries slices of long units next to whole units hashes the two as two kernels: the slices on
+    // s_batch (the next batch's slices wait for ev_slice only), the whole units beside them on s_aux
+    cudaStream_t s_aux[NBUF] = {};
+    cudaEvent_t ev_copied[NBUF] = {}, ev_slice[NBUF] = {}, ev_aux[NBUF] = {};
     bool buf_free[NBUF];
     int n_free = NBUF;
     int active_calls = 0;                // host calls that hold a lease on this slot right now
@@ -512,6 +516,9 @@ static int ensure_buffer(tpimd5_ctx *ctx, Slot &s, int i, bool need_host) {
         CU(cudaHostAlloc(&s.h_desc_raw[i], MAX_BATCH_LANES * desc_bytes_per_lane, cudaHostAllocDefault));
         CU(cudaMalloc(&s.d_desc_raw[i], MAX_BATCH_LANES * desc_bytes_per_lane));
         CU(cudaEventCreateWithFlags(&s.ev_done[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&s.ev_copied[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&s.ev_slice[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&s.ev_aux[i], cudaEventDisableTiming));
     }
     if (need_host && !s.h_stage[i]) CU(cudaHostAlloc(&s.h_stage[i], s.stage_bytes + 256, cudaHostAllocDefault));
     return 0;
@@ -550,6 +557,7 @@ extern "C" int tpimd5_init(const int *device_ids, int n_devices, size_t staging_
         USE_DEVICE(dev);
         CU(cudaStreamCreateWithFlags(&s->s_comp, cudaStreamNonBlocking));
         for (int b = 0; b < NBUF; ++b) CU(cudaStreamCreateWithFlags(&s->s_batch[b], cudaStreamNonBlocking));
+        for (int b = 0; b < NBUF; ++b) CU(cudaStreamCreateWithFlags(&s->s_aux[b], cudaStreamNonBlocking));
         ctx->slots.push_back(std::move(s));
     }
     if (const char *e = getenv("TPIMD5_ROW_MAX")) {
@@ -578,12 +586,17 @@ extern "C" void tpimd5_destroy(tpimd5_ctx *ctx) {
         if (s.s_comp) cudaStreamSynchronize(s.s_comp);
         for (int b = 0; b < NBUF; ++b)
             if (s.s_batch[b]) { cudaStreamSynchronize(s.s_batch[b]); cudaStreamDestroy(s.s_batch[b]); }
+        for (int b = 0; b < NBUF; ++b)
+            if (s.s_aux[b]) { cudaStreamSynchronize(s.s_aux[b]); cudaStreamDestroy(s.s_aux[b]); }
         for (int i = 0; i < NBUF; ++i) {
             if (s.h_stage[i]) cudaFreeHost(s.h_stage[i]);
             if (s.d_stage[i]) cudaFree(s.d_stage[i]);
             if (s.h_desc_raw[i]) cudaFreeHost(s.h_desc_raw[i]);
             if (s.d_desc_raw[i]) cudaFree(s.d_desc_raw[i]);
             if (s.ev_done[i]) cudaEventDestroy(s.ev_done[i]);
+            if (s.ev_copied[i]) cudaEventDestroy(s.ev_copied[i]);
+            if (s.ev_slice[i]) cudaEventDestroy(s.ev_slice[i]);
+            if (s.ev_aux[i]) cudaEventDestroy(s.ev_aux[i]);
         }
         for (TableBuf &t : s.free_tables) { cudaFree(t.d); cudaFreeHost(t.h); }
         for (DevBlock &b : s.free_blocks) cudaFree(b.d);
@@ -1359,8 +1372,10 @@ struct Lease {
         }
     }
     ~Lease() {
-        for (int bi : bufs)
+        for (int bi : bufs) {
+            if (s.s_aux[bi]) cudaStreamSynchronize(s.s_aux[bi]);
             if (s.s_batch[bi]) cudaStreamSynchronize(s.s_batch[bi]);
+        }
         if (stream) cudaStreamSynchronize(stream);
         give_table(s, table);
         give_stream(s, stream);
@@ -1474,7 +1489,71 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
     std::atomic<int> io_err{0};
     std::atomic<size_t> io_idx{(size_t)-1};
 
-    while (ui < nu) {
+    // Packed batches (files, scattered or pageable units) take LONG units in slices, many units side by side:
+    // a unit is one serial chain (~160 MB/s once its bytes are on the device), so a long unit that arrives
+    // whole, after the ones before it, finishes its-length / chain-rate after everything before it was read
+    // (the last 8 MiB part of a multipart object: 53 ms after the file's last byte; the tenth 1 GiB file of a
+    // workdir: after nine others' chains).  Sliced, every long unit's chain starts in the first batches and
+    // keeps pace with the reads; a batch's kernel then runs for slice / chain-rate, which the slice bounds
+    // below set to about the time the batch takes to read and copy (256 MiB at ~43 GB/s ~ 1 MiB of chain).
+    struct Active { uint32_t ui; uint64_t consumed; int last_bi; };
+    std::vector<Active> active;
+    // Which units are sliced: always those above half a staging buffer; from 4 MiB when whole units in listing
+    // order would end later than slices do by these estimates (reads + copies ~40 GB/s, one chain ~0.16 GB/s):
+    //   whole units:  the latest (everything up to and including unit i read) + (unit i's chain)
+    //   slices:       max(everything read, the longest chain) + one slice's chain
+    // Whole units win when a few long chains bound the call and come first anyway (a workdir of files up to 8 MiB,
+    // longest first); slices win when many equal long units arrive one after another (the parts of one object).
+    uint64_t stripe_min = s.stage_bytes / 2;
+    // How many units are sliced side by side.  A batch of A slices takes A x slice / 40 GB/s to read and copy and
+    // slice / 0.16 GB/s to hash, and each batch's slices wait for the previous batch's: with 256 the kernels
+    // just keep up with full-speed reads and a chain gets its bytes at the rate it can hash them -- right when the
+    // longest chain bounds the call.  When the reads bound it, 384 thinner slices keep the kernels ahead of them
+    // (an 8 GiB object in 8 MiB parts: the kernels finished 31 ms after the last read with 256, 5 ms with 384).
+    size_t max_active = 256;
+    if (!direct) {
+        const uint64_t cand = std::min<uint64_t>((uint64_t)4 << 20, s.stage_bytes / 4);
+        constexpr size_t CHUNK = 1u << 16;
+        std::atomic<uint64_t> a_total{0}, a_max{0}, a_long{0};
+        std::function<void(size_t)> sum = [&](size_t c) {
+            uint64_t t = 0, m = 0, nl = 0;
+            const size_t hi = std::min(nu, (c + 1) * CHUNK);
+            for (size_t i = c * CHUNK; i < hi; ++i) {
+                const uint64_t l = job.len[units[i]];
+                t += l; m = std::max(m, l); nl += l >= cand;
+            }
+            a_total.fetch_add(t); a_long.fetch_add(nl);
+            uint64_t cur = a_max.load();
+            while (m > cur && !a_max.compare_exchange_weak(cur, m)) {}
+        };
+        ctx->pool->parallel_for((nu + CHUNK - 1) / CHUNK, 1, sum);
+        if (a_long.load() > 1 && a_max.load() < stripe_min) {
+            const double R = 40e9, r = 0.16e9, total = (double)a_total.load();
+            double whole = total / R, pre = 0;
+            for (size_t i = 0; i < nu; ++i) {
+                const uint64_t l = job.len[units[i]];
+                pre += (double)l;
+                if (l >= cand) whole = std::max(whole, pre / R + (double)l / r);
+                else if (from_files) break;                       // files come longest first
+            }
+            const double sliced = std::max(total / R, (double)a_max.load() / r) + (double)(s.stage_bytes / 256) / r;
+            if (whole > 1.08 * sliced) stripe_min = cand;
+            if (total / R > (double)a_max.load() / r) {
+                // ... in equal groups, so that the last group is not a short one whose chains outlast its reads
+                const size_t groups = (a_long.load() + 383) / 384;
+                max_active = std::max<size_t>(256, (a_long.load() + groups - 1) / groups);
+            }
+        } else if (a_long.load() > 1) {
+            stripe_min = cand;      // units above half a buffer are sliced anyway: the other long ones go with them
+        }
+    }
+    size_t next_long = 0, next_short = 0;      // scan positions in `units` for the two classes
+    auto skip_long = [&] { while (next_long < nu && job.len[units[next_long]] < stripe_min) ++next_long; };
+    auto skip_short = [&] { while (next_short < nu && job.len[units[next_short]] >= stripe_min) ++next_short; };
+    if (!direct) { skip_long(); skip_short(); }
+    auto more = [&] { return direct ? ui < nu : (!active.empty() || next_long < nu || next_short < nu); };
+
+    while (more()) {
         // ---- a staging buffer: a fresh one, or this call's oldest once its batch has been consumed ----
         const double tr_w0 = trace_now();
         int bi = -1;
@@ -1497,7 +1576,54 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
         uint64_t lo = 0;         // direct mode: caller offset of the batch's first byte ...
         uint64_t shift = 0;      // ... which lands at this staging offset (keeps offsets' alignment mod 16)
         bool have_lo = false;
-        while (ui < nu && pieces.size() < MAX_BATCH_LANES) {
+        uint32_t dep_bufs = 0;   // staging buffers whose kernels wrote chaining values this batch continues from
+        size_t ns = 0;           // pieces [0, ns) are slices of long units, [ns, np) whole short units
+        if (!direct) {
+            const bool shorts_left = next_short < nu;
+            while (active.size() < max_active && next_long < nu) {
+                active.push_back({(uint32_t)next_long, 0, -1});
+                ++next_long;
+                skip_long();
+            }
+            if (!active.empty()) {
+                // with short units still to come the slice is what a chain hashes while a batch is read and copied
+                // (the short units fill the rest of the buffer); once only long units are left, the whole buffer
+                const uint64_t lo_s = (cap / max_active - 16) & ~(uint64_t)63;
+                const uint64_t slice = shorts_left ? lo_s : std::max(lo_s, (cap / active.size() - 16) & ~(uint64_t)63);
+                for (Active &a : active) {
+                    if (pieces.size() >= MAX_BATCH_LANES) break;
+                    const uint64_t ulen = job.len[units[a.ui]];
+                    const uint64_t rem = ulen - a.consumed;
+                    const uint64_t spare = from_files ? 1 : 0;              // files: one spare byte for the grew-since-listing probe
+                    const bool fin = rem + spare <= slice;
+                    uint64_t take = fin ? rem : std::min(rem, slice) & ~(uint64_t)63;
+                    if (!fin && take == rem) take -= 64;                    // never a final piece of no bytes
+                    const uint64_t extra = fin ? spare : 0;
+                    const uint64_t dst = (used + 15) & ~(uint64_t)15;
+                    if (dst + take + extra > cap) break;                   // the rest of the active units wait a batch
+                    if (a.consumed > 0 && a.last_bi >= 0) dep_bufs |= 1u << a.last_bi;
+                    pieces.push_back({a.ui, a.consumed, take, dst, fin});
+                    used = dst + take + extra;
+                    a.consumed += take;
+                    a.last_bi = bi;
+                    if (fin) a.last_bi = -2;                                // done: dropped below
+                }
+                active.erase(std::remove_if(active.begin(), active.end(), [](const Active &a) { return a.last_bi == -2; }), active.end());
+            }
+            ns = pieces.size();
+            while (next_short < nu && pieces.size() < MAX_BATCH_LANES) {
+                const uint64_t ulen = job.len[units[next_short]];
+                const uint64_t dst = (used + 15) & ~(uint64_t)15;
+                // (a first batch is capped below a buffer; a unit under half a buffer still goes in whole)
+                if (dst + ulen + (from_files ? 1 : 0) > (pieces.empty() ? s.stage_bytes : cap)) break;
+                pieces.push_back({(uint32_t)next_short, 0, ulen, dst, true});
+                used = dst + ulen + (from_files ? 1 : 0);
+                ++next_short;
+                skip_short();
+            }
+            if (pieces.empty()) return fail(TPIMD5_EINVAL, "internal: a batch without units");
+        }
+        while (direct && ui < nu && pieces.size() < MAX_BATCH_LANES) {
             const uint32_t u = units[ui];
             const uint64_t ulen = job.len[u];
             const uint64_t rem = ulen - consumed;
@@ -1530,11 +1656,16 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
         tr_plan += trace_now() - tr_b0;
 
         // ---- lanes, longest first so that a warp's 32 units finish together ---------------------
+        // (slices and whole units are two launches: each group is ordered by itself)
         order.resize(np);
         for (size_t i = 0; i < np; ++i) order[i] = (uint32_t)i;
         bool ragged = false;
-        for (size_t i = 1; i < np && !ragged; ++i) ragged = (pieces[i].len >> 6) != (pieces[0].len >> 6);
-        if (ragged) std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return pieces[a].len > pieces[b].len; });
+        for (size_t g0 = 0, g1 = ns ? ns : np; g0 < np; g0 = g1, g1 = np) {
+            bool rg = false;
+            for (size_t i = g0 + 1; i < g1 && !rg; ++i) rg = (pieces[i].len >> 6) != (pieces[g0].len >> 6);
+            if (rg) std::stable_sort(order.begin() + g0, order.begin() + g1, [&](uint32_t a, uint32_t b) { return pieces[a].len > pieces[b].len; });
+            ragged = ragged || rg;
+        }
         // the five descriptor arrays are carved for exactly np lanes, so they are one contiguous copy
         LaneDesc h, dv;
         carve_desc(s.h_desc_raw[bi], np, h);
@@ -1549,7 +1680,7 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
         // A batch of whole, fresh units of one length at one spacing (a workdir of equal small files, the parts of
         // one S3 object) needs no per-unit descriptors at all: it is described to the TMA unit as a 2-D tensor and
         // goes to the strided kernels (throughput or latency kernel by launch size), like device-resident input.
-        bool uniform = np >= 1 && !ragged && !job.init_states && !job.nonfinal && !job.prior && tma_loader >= 2;
+        bool uniform = np >= 1 && ns == 0 && !ragged && !job.init_states && !job.nonfinal && !job.prior && tma_loader >= 2;
         uint64_t ustride = 0;
         if (uniform) {
             const uint64_t ulen = pieces[0].len;
@@ -1686,15 +1817,37 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
         // ---- hash (same stream: the kernel follows its batch's copies) -----------------------------
         cudaStream_t sk = s.s_batch[bi];
         // a unit continued from the previous batch reads the chaining value that batch's kernel writes
-        if (batch > 0 && np && pieces[0].src_off > 0) CU(cudaStreamWaitEvent(sk, s.ev_done[prev_bi], 0));
-        LaneArgs a{};
-        a.base = s.d_stage[bi]; a.base_bytes = used;
-        a.off = dv.off; a.len = dv.len; a.prior = dv.prior;
-        a.flags = dv.flags; a.out_idx = dv.oidx;
-        a.table = d_table; a.n = np;
-        if (uniform) rc = launch_strided_tma(ctx, s.d_stage[bi] + pieces[0].dst, ustride, pieces[0].len, np, d_table + pieces[0].unit,
-                                             tma_loader, tma_shape, tma_mode, sk);
-        else rc = launch_lanes(ctx, a, aligned, sk);
+        if (direct && batch > 0 && np && pieces[0].src_off > 0) CU(cudaStreamWaitEvent(sk, s.ev_done[prev_bi], 0));
+        auto lanes_of = [&](size_t g0, size_t g1) {
+            LaneArgs a{};
+            a.base = s.d_stage[bi]; a.base_bytes = used;
+            a.off = dv.off + g0; a.len = dv.len + g0; a.prior = dv.prior + g0;
+            a.flags = dv.flags + g0; a.out_idx = dv.oidx + g0;
+            a.table = d_table; a.n = g1 - g0;
+            return a;
+        };
+        if (uniform) {
+            rc = launch_strided_tma(ctx, s.d_stage[bi] + pieces[0].dst, ustride, pieces[0].len, np, d_table + pieces[0].unit,
+                                    tma_loader, tma_shape, tma_mode, sk);
+        } else if (ns == 0) {
+            rc = launch_lanes(ctx, lanes_of(0, np), aligned, sk);
+        } else {
+            // whole units beside the slices, on the buffer's second stream, once the batch's bytes are in place
+            if (np > ns) {
+                CU(cudaEventRecord(s.ev_copied[bi], sk));
+                CU(cudaStreamWaitEvent(s.s_aux[bi], s.ev_copied[bi], 0));
+                rc = launch_lanes(ctx, lanes_of(ns, np), aligned, s.s_aux[bi]);
+                if (rc) return rc;
+                CU(cudaEventRecord(s.ev_aux[bi], s.s_aux[bi]));
+            }
+            // the slices: after the kernels that wrote the chaining values they continue from
+            for (int b = 0; b < NBUF; ++b)
+                if ((dep_bufs >> b & 1) && b != bi) CU(cudaStreamWaitEvent(sk, s.ev_slice[b], 0));
+            rc = launch_lanes(ctx, lanes_of(0, ns), aligned, sk);
+            if (rc) return rc;
+            CU(cudaEventRecord(s.ev_slice[bi], sk));
+            if (np > ns) CU(cudaStreamWaitEvent(sk, s.ev_aux[bi], 0));
+        }
         if (rc) return rc;
         CU(cudaEventRecord(s.ev_done[bi], sk));
         for (size_t i = 0; i < np; ++i) batch_bytes += pieces[i].len;

@@ -132,6 +132,52 @@ def test_s3_etag_file_and_hash_files(ctx, tmp_path):
         ctx.hash_files(paths + [str(tmp_path / "missing")])
 
 
+@pytest.mark.parametrize("staging", [1 << 20, 4 << 20])
+def test_long_units_are_hashed_in_slices_side_by_side(tmp_path, staging):
+    """The packed path takes long units in slices, up to 384 of them side by side, each batch's slices continuing
+    from the previous batch's chaining values while whole short units ride in the same buffers as a second launch
+    (run_device_impl, csrc/tpimd5.cu).  Small staging buffers put every case of that planner within a few MiB:
+    units above half a buffer (always sliced), many equal long units (the parts of one object: sliced because
+    whole units in order would end later), more long units than are active at once, lengths that end exactly on a
+    slice, on a slice + 1 and on a 64-byte multiple, files that grew or shrank in a sliced unit."""
+    rng = np.random.default_rng(staging)
+    sizes = [0, 1, 63, 64, 65, 4096, staging // 2 - 1, staging // 2, staging // 2 + 1, staging, staging + 1, 3 * staging + 77,
+             7 * staging, staging // 4, staging // 4 + 64, 2 * staging + 64]
+    sizes += [int(x) for x in rng.integers(0, 3000, 300)] + [int(x) for x in rng.integers(staging // 4, staging, 40)]
+    blob = oracle.synth_bytes(31, 0, max(sizes) + len(sizes))
+    paths = []
+    for i, n in enumerate(sizes):
+        p = tmp_path / f"u{i}.bin"
+        p.write_bytes(blob[i:i + n].tobytes())
+        paths.append(str(p))
+    want = np.stack([np.frombuffer(oracle.md5(blob[i:i + n]), dtype=np.uint8) for i, n in enumerate(sizes)])
+    with tpi.Context([0], staging_bytes=staging) as c:
+        assert np.array_equal(c.hash_files(paths, sizes), want)
+        assert np.array_equal(c.hash_files(paths), want)
+        # the same units out of pageable memory (packed), in caller order rather than longest first
+        off = np.cumsum([0] + [n + 3 for n in sizes[:-1]]).astype(np.uint64)
+        buf = np.zeros(int(off[-1]) + sizes[-1], dtype=np.uint8)
+        for i, n in enumerate(sizes):
+            buf[int(off[i]):int(off[i]) + n] = blob[i:i + n]
+        assert np.array_equal(c.hash_buffers(buf, off, np.array(sizes, dtype=np.uint64)), want)
+        # the parts of one object: 500 equal long units and a ragged last one, more than are active at once
+        part = staging // 4 + 128
+        size = 500 * part + 12345
+        obj = tmp_path / "object.bin"
+        data = oracle.synth_files(32, 0, size, 1, threads=8)
+        obj.write_bytes(data.tobytes())
+        etag, n, parts = c.s3_etag_file(str(obj), size, part)
+        o = oracle.s3_etag(data, part, threads=8)
+        assert (etag, n) == (o[0], o[1]) and np.array_equal(parts, o[2])
+        # a sliced file that is longer / shorter than listed is an error that names it
+        for delta in (1, -1):
+            listed = list(sizes)
+            listed[12] += delta
+            with pytest.raises(tpi.TpiMd5Error) as e:
+                c.hash_files(paths, listed)
+            assert e.value.code == -4 and e.value.failed_index == 12
+
+
 def test_stream_is_a_go_hash(ctx):
     data = oracle.synth_bytes(26, 0, (9 << 20) + 13).tobytes()
     s, o = ctx.stream(), oracle.MD5Stream()
