@@ -1537,7 +1537,8 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
                 else if (from_files) break;                       // files come longest first
             }
             const double sliced = std::max(total / R, (double)a_max.load() / r) + (double)(s.stage_bytes / 256) / r;
-            if (whole > 1.08 * sliced) stripe_min = cand;
+            static const int force = [] { const char *e = getenv("TPIMD5_SLICE"); return e ? atoi(e) : -1; }();   // diagnostics: 1 always, 0 never
+            if (force < 0 ? whole > 1.08 * sliced : force == 1) stripe_min = cand;
             if (total / R > (double)a_max.load() / r) {
                 // ... in equal groups, so that the last group is not a short one whose chains outlast its reads
                 const size_t groups = (a_long.load() + 383) / 384;
