@@ -58,8 +58,8 @@ CHAIN_FLOOR_CYCLES = 768          # 64 steps x three dependent 4-cycle integer o
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=100)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--variant", type=int, default=int(os.environ.get("TPIMD5_VARIANT", "0")))
     ap.add_argument("--files", type=int, default=FILES_PER_GPU, help="files per GPU (default: the C2 size)")
