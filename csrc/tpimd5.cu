@@ -391,6 +391,10 @@ struct tpimd5_ctx {
     std::atomic<int> variant{0};
     // what tpimd5_get_progress reports (monotonic since tpimd5_init)
     std::atomic<uint64_t> calls_started{0}, calls_finished{0}, units_done{0}, bytes_staged{0}, bytes_done{0};
+    // measured rate at which packed batches fill (bytes per second into pinned staging; a running mean over
+    // batches of >= 16 MiB), from files and from caller memory: what the slice planner weighs chains against.
+    // Starts at the page-cache rate of the boxes this was tuned on; a slow disk brings it down within a call.
+    std::atomic<double> feed_files{40e9}, feed_mem{40e9};
     // longest tensor-map row, and bytes of a longer unit hashed per launch (tests shrink both through the
     // environment to run the segment logic on small data)
     uint64_t row_max = (uint64_t)1 << 31, chain_seg = (uint64_t)1 << 30;
@@ -1499,7 +1503,8 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
     struct Active { uint32_t ui; uint64_t consumed; int last_bi; };
     std::vector<Active> active;
     // Which units are sliced: always those above half a staging buffer; from 4 MiB when whole units in listing
-    // order would end later than slices do by these estimates (reads + copies ~40 GB/s, one chain ~0.16 GB/s):
+    // order would end later than slices do by these estimates (reads at the context's measured fill rate, ~40 GB/s
+    // from the page cache; one chain ~0.16 GB/s):
     //   whole units:  the latest (everything up to and including unit i read) + (unit i's chain)
     //   slices:       max(everything read, the longest chain) + one slice's chain
     // Whole units win when a few long chains bound the call and come first anyway (a workdir of files up to 8 MiB,
@@ -1528,7 +1533,7 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
         };
         ctx->pool->parallel_for((nu + CHUNK - 1) / CHUNK, 1, sum);
         if (a_long.load() > 1 && a_max.load() < stripe_min) {
-            const double R = 40e9, r = 0.16e9, total = (double)a_total.load();
+            const double R = std::max(0.05e9, (from_files ? ctx->feed_files : ctx->feed_mem).load()), r = 0.16e9, total = (double)a_total.load();
             double whole = total / R, pre = 0;
             for (size_t i = 0; i < nu; ++i) {
                 const uint64_t l = job.len[units[i]];
@@ -1807,7 +1812,12 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
             // call start; once the pipeline streams, the extra copies just take memory bandwidth from the readers:
             // an 8 GiB file went 250 -> 262 ms with slices on every batch, C1 72 -> 70 ms either way.)
             ctx->pool->parallel_for(tasks.size(), 1, fill_mark, (used >= (64u << 20) && batch < 6 && longest >= (1u << 20)) ? &tick : nullptr);
-            tr_fill += trace_now() - tr_f0;
+            const double fill_s = trace_now() - tr_f0;
+            tr_fill += fill_s;
+            if (used >= (16u << 20) && fill_s > 0) {
+                std::atomic<double> &rate = from_files ? ctx->feed_files : ctx->feed_mem;
+                rate.store(0.5 * rate.load() + 0.5 * ((double)used / fill_s));
+            }
             if (io_err.load() != 0) break;
             if (copy_err != cudaSuccess) return fail(TPIMD5_ECUDA, "cudaMemcpyAsync (staging): %s", cudaGetErrorString(copy_err));
             if (used > sent) CU(cudaMemcpyAsync(s.d_stage[bi] + sent, stage + sent, used - sent, cudaMemcpyHostToDevice, s.s_batch[bi]));
