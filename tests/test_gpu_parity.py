@@ -426,6 +426,37 @@ def test_zipf_sizes_config4_shape_scaled():
     assert np.array_equal(got, want)
 
 
+def test_sliced_calls_from_many_threads_share_the_staging_buffers():
+    """Eight threads, one context with 1 MiB staging buffers, every call with units of several buffers' length: the
+    slices of a call continue from chaining values written by kernels in buffers that are meanwhile leased, handed
+    back and taken by other calls; each call's digests must still be its own."""
+    import threading
+    stage = 1 << 20
+    jobs = []
+    for k in range(8):
+        rng = np.random.default_rng(500 + k)
+        lengths = [int(x) for x in rng.integers(0, 4000, 150)] + [int(x) for x in rng.integers(stage // 4, 5 * stage, 6)] + [3 * stage + k]
+        rng.shuffle(lengths)
+        buf, off, ln = oracle.synth_packed(500 + k, lengths, align=1)
+        jobs.append((buf, off, ln, oracle.md5_batch(buf, off, ln, threads=2)))
+    errs = []
+    with tpi.Context([0], staging_bytes=stage) as c:
+        def worker(k):
+            try:
+                buf, off, ln, want = jobs[k]
+                for _ in range(2):
+                    got = c.hash_buffers(buf, off, ln)
+                    bad = np.nonzero((got != want).any(axis=1))[0]
+                    assert bad.size == 0, (k, bad[:4], ln[bad[:4]])
+            except Exception as e:      # noqa: BLE001
+                errs.append(e)
+
+        th = [threading.Thread(target=worker, args=(k,)) for k in range(8)]
+        [t.start() for t in th]
+        [t.join() for t in th]
+    assert not errs, errs
+
+
 def test_one_context_many_threads(ctx):
     """Terraform runs resource operations concurrently in one plugin process and rclone hashes from
     8 checker + 4 transfer goroutines: a context must take calls from many threads at once."""
