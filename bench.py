@@ -662,7 +662,12 @@ def run_c1(env):
                 oracle.md5_files(both, threads=th, engine=eng)
             cpu[label] = round(reps * (2 << 30) / (time.perf_counter() - t0) / 1e9, 3)
         mean = sum(t_gpu) / reps
-        return {"workload": "C1: 1,000 files / 1 GiB on tmpfs, machine.Transfer local->local with --checksum, unchanged second "
+        both_sizes = np.concatenate([sizes, sizes]).astype(np.uint64)
+        ceiling = ingest_ceiling(ctx, env.tpi.PathList(both), both_sizes, 2 << 30, (2 << 30) / mean / 1e9)
+        longest = int(sizes.max())
+        ceiling["longest_file_chain_ms"] = round(1e3 * longest / 0.161e9, 1)       # one file = one serial chain (~0.161 GB/s)
+        return {"ceiling": ceiling,
+                "workload": "C1: 1,000 files / 1 GiB on tmpfs, machine.Transfer local->local with --checksum, unchanged second "
                             "pass (2 GiB hashed: both sides); end to end: listing, file reads, H2D, kernels, D2H, plan",
                 "value": round((2 << 30) / mean / 1e9, 3), "unit": "GB/s", "steps": reps, "warmup": 1,
                 "ms_per_step": round(1e3 * mean, 2), "best_ms": round(1e3 * min(t_gpu), 2),
@@ -673,6 +678,21 @@ def run_c1(env):
                                            f"{cpu['all_cores']} GB/s on {os.cpu_count()} threads"}}
     finally:
         shutil.rmtree(root, ignore_errors=True)
+
+
+def ingest_ceiling(ctx, listing, sizes, nbytes, value_gbps, file_offsets=None, reps=3):
+    """SURVEY 8d "end-to-end ceiling (a)": the same listing read into the same pinned staging buffers by the same
+    reader threads with nothing copied to the device and nothing hashed (tpimd5_ingest_probe), in the same run."""
+    ctx.ingest_probe(listing, sizes, file_offsets)
+    t = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        ctx.ingest_probe(listing, sizes, file_offsets)
+        t.append(time.perf_counter() - t0)
+    mean = sum(t) / reps
+    ceil = nbytes / mean / 1e9
+    return {"host_ingest_GBps": round(ceil, 3), "ms": round(1e3 * mean, 1), "frac_of_host_ingest": round(value_gbps / ceil, 3),
+            "how": "tpimd5_ingest_probe: open/read/close of the same listing into pinned staging, no H2D, no kernels"}
 
 
 def run_c2_files(env, n=200_000):
@@ -720,7 +740,9 @@ def run_c2_files(env, n=200_000):
         if not np.array_equal(got, want):
             raise SystemExit("bench.py: c2_files digests differ from the CPU path's")
         mean, cmean = sum(t) / 3, sum(tc) / 3
-        return {"workload": f"C2 from real files: {n:,} x 4 KiB files, 1,024-way directory fan-out on tmpfs, tpimd5_hash_files "
+        ceiling = ingest_ceiling(ctx, listing, sizes, n * FILE_BYTES, n * FILE_BYTES / mean / 1e9)
+        return {"ceiling": ceiling,
+                "workload": f"C2 from real files: {n:,} x 4 KiB files, 1,024-way directory fan-out on tmpfs, tpimd5_hash_files "
                             "(open/read/close + H2D + kernel + D2H)",
                 "value": round(n * FILE_BYTES / mean / 1e9, 3), "unit": "GB/s", "files_per_s": round(n / mean), "steps": 3,
                 "warmup": 1, "ms_per_step": round(1e3 * mean, 1), "best_ms": round(1e3 * min(t), 1), "gpu_launches": launches,
@@ -766,7 +788,11 @@ def run_c3_file(env, size=(8 << 30) + 12345, part=8 << 20):
         if (etag, n) != (o_etag, o_n) or not np.array_equal(parts, o_parts):
             raise SystemExit("bench.py: c3_file ETag differs from the CPU path's")
         mean = sum(t) / 3
-        return {"workload": f"C3 from a real file: one {size / 2**30:.1f} GiB checkpoint on tmpfs, S3 multipart ETag with 8 MiB parts "
+        offs = np.arange(n, dtype=np.uint64) * np.uint64(part)
+        lens = np.minimum(np.uint64(size) - offs, np.uint64(part))
+        ceiling = ingest_ceiling(ctx, env.tpi.PathList([path] * n), lens, size, size / mean / 1e9, file_offsets=offs)
+        return {"ceiling": ceiling,
+                "workload": f"C3 from a real file: one {size / 2**30:.1f} GiB checkpoint on tmpfs, S3 multipart ETag with 8 MiB parts "
                             f"({n} parts, the last one ragged), tpimd5_s3_etag_file (reads + H2D + kernels + D2H)",
                 "value": round(size / mean / 1e9, 3), "unit": "GB/s", "steps": 3, "warmup": 1, "ms_per_step": round(1e3 * mean, 1),
                 "best_ms": round(1e3 * min(t), 1), "etag": env.tpi.s3_etag_text(etag, n), "gpu_launches": launches,

@@ -1232,6 +1232,7 @@ struct Job {
     const uint8_t *nonfinal = nullptr;     // per unit: 1 = leave as chaining value; or null
     uint8_t *out = nullptr;
     size_t failed_index = (size_t)-1;
+    bool ingest_only = false;              // tpimd5_ingest_probe: plan and fill the staging buffers, copy and hash nothing
 };
 
 struct Piece {
@@ -1802,7 +1803,7 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
                 while (cursor < n_data && task_done[cursor].load(std::memory_order_acquire)) ++cursor;
                 if (!cursor || copy_err != cudaSuccess || io_err.load() != 0) return;
                 const uint64_t upto = std::min<uint64_t>(task_end[cursor - 1], used) & ~(uint64_t)15;
-                if (upto >= sent + (16u << 20) && cursor < n_data) {
+                if (upto >= sent + (16u << 20) && cursor < n_data && !job.ingest_only) {
                     copy_err = cudaMemcpyAsync(s.d_stage[bi] + sent, stage + sent, upto - sent, cudaMemcpyHostToDevice, s.s_batch[bi]);
                     sent = upto;
                 }
@@ -1820,10 +1821,10 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
             }
             if (io_err.load() != 0) break;
             if (copy_err != cudaSuccess) return fail(TPIMD5_ECUDA, "cudaMemcpyAsync (staging): %s", cudaGetErrorString(copy_err));
-            if (used > sent) CU(cudaMemcpyAsync(s.d_stage[bi] + sent, stage + sent, used - sent, cudaMemcpyHostToDevice, s.s_batch[bi]));
+            if (used > sent && !job.ingest_only) CU(cudaMemcpyAsync(s.d_stage[bi] + sent, stage + sent, used - sent, cudaMemcpyHostToDevice, s.s_batch[bi]));
         }
         // descriptors: five arrays, copied as stored (their device mirror has the same carving)
-        if (np && !uniform) CU(cudaMemcpyAsync(s.d_desc_raw[bi], s.h_desc_raw[bi], np * desc_bytes_per_lane, cudaMemcpyHostToDevice, s.s_batch[bi]));
+        if (np && !uniform && !job.ingest_only) CU(cudaMemcpyAsync(s.d_desc_raw[bi], s.h_desc_raw[bi], np * desc_bytes_per_lane, cudaMemcpyHostToDevice, s.s_batch[bi]));
 
         // ---- hash (same stream: the kernel follows its batch's copies) -----------------------------
         cudaStream_t sk = s.s_batch[bi];
@@ -1837,7 +1838,9 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
             a.table = d_table; a.n = g1 - g0;
             return a;
         };
-        if (uniform) {
+        if (job.ingest_only) {
+            rc = 0;
+        } else if (uniform) {
             rc = launch_strided_tma(ctx, s.d_stage[bi] + pieces[0].dst, ustride, pieces[0].len, np, d_table + pieces[0].unit,
                                     tma_loader, tma_shape, tma_mode, sk);
         } else if (ns == 0) {
@@ -1884,6 +1887,10 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
 
     // ---- digests home -------------------------------------------------------------------------
     for (int b : lease.bufs) CU(cudaStreamWaitEvent(lease.stream, s.ev_done[b], 0));
+    if (job.ingest_only) {
+        CU(cudaStreamSynchronize(lease.stream));
+        return 0;
+    }
     CU(cudaMemcpyAsync(h_table, d_table, nu * 16, cudaMemcpyDeviceToHost, lease.stream));
     const double tr_s0 = trace_now();
     CU(cudaStreamSynchronize(lease.stream));
@@ -2010,6 +2017,19 @@ extern "C" int tpimd5_hash_buffers(tpimd5_ctx *ctx, const uint8_t *base, const u
     Job job;
     job.n = n; job.base = base; job.off = offsets; job.len = lengths; job.out = digests_out;
     return run_job(ctx, job);
+}
+
+extern "C" int tpimd5_ingest_probe(tpimd5_ctx *ctx, const char *const *paths, const uint64_t *file_offsets, const uint64_t *sizes, size_t n,
+                                   size_t *failed_index_out) {
+    if (failed_index_out) *failed_index_out = (size_t)-1;
+    if (!ctx) return fail(TPIMD5_EINVAL, "ingest_probe: null context");
+    if (n == 0) return 0;
+    if (!paths || !sizes) return fail(TPIMD5_EINVAL, "ingest_probe: null pointer");
+    Job job;
+    job.n = n; job.len = sizes; job.paths = paths; job.file_off = file_offsets; job.ingest_only = true;
+    int rc = run_job(ctx, job);
+    if (rc && failed_index_out) *failed_index_out = job.failed_index;
+    return rc;
 }
 
 extern "C" int tpimd5_units_extent(tpimd5_ctx *ctx, const uint64_t *offsets, const uint64_t *lengths, size_t n, uint64_t *extent_out) {

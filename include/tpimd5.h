@@ -86,6 +86,12 @@ TPIMD5_API int tpimd5_hash_files(tpimd5_ctx *ctx, const char *const *paths, cons
  * lengths[i] (0 for n == 0), computed on the context's worker pool -- what a cgo / ctypes wrapper compares with the
  * length of the slice it was handed before it passes `base` to tpimd5_hash_buffers, which cannot know it.
  * TPIMD5_ERANGE if an offset + length overflows 64 bits. */
+/* Diagnostic (no reference counterpart): the host-ingest ceiling of tpimd5_hash_files and tpimd5_s3_etag_file on this
+ * box.  Plans the same batches and lets the same reader threads fill the same pinned staging buffers -- bytes
+ * [file_offsets[i], + sizes[i]) of paths[i]; file_offsets may be NULL = whole files -- and stops there: nothing is
+ * copied to the device, nothing is hashed, no digests come back.  bench.py quotes the end-to-end rates against it. */
+TPIMD5_API int tpimd5_ingest_probe(tpimd5_ctx *ctx, const char *const *paths, const uint64_t *file_offsets, const uint64_t *sizes,
+                                   size_t n, size_t *failed_index_out);
 TPIMD5_API int tpimd5_units_extent(tpimd5_ctx *ctx, const uint64_t *offsets, const uint64_t *lengths, size_t n, uint64_t *extent_out);
 
 /* ---- S3 multipart ------------------------------------------------------------------------

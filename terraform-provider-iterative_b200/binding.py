@@ -19,7 +19,7 @@ _lib: Optional[C.CDLL] = None
 EXPORTS = [
     "tpimd5_device_count", "tpimd5_init", "tpimd5_destroy", "tpimd5_ctx_devices", "tpimd5_get_progress", "tpimd5_last_error",
     "tpimd5_version", "tpimd5_hash_buffers", "tpimd5_hash_files", "tpimd5_s3_part_size", "tpimd5_s3_nparts",
-    "tpimd5_s3_etag_buffer", "tpimd5_s3_etag_file", "tpimd5_s3_plan_parts", "tpimd5_units_extent", "tpimd5_s3_upload_plan", "tpimd5_stream_open", "tpimd5_stream_write",
+    "tpimd5_s3_etag_buffer", "tpimd5_s3_etag_file", "tpimd5_s3_plan_parts", "tpimd5_units_extent", "tpimd5_ingest_probe", "tpimd5_s3_upload_plan", "tpimd5_stream_open", "tpimd5_stream_write",
     "tpimd5_stream_write_many", "tpimd5_stream_sum", "tpimd5_stream_reset", "tpimd5_stream_close", "tpimd5_diff",
     "tpimd5_dev_hash_buffers", "tpimd5_dev_s3_etag", "tpimd5_dev_diff", "tpimd5_dev_synth_fill",
     "tpimd5_dev_s3_etag_noalloc", "tpimd5_filter_new", "tpimd5_filter_free", "tpimd5_filter_include", "tpimd5_filter_include_dir",
@@ -68,6 +68,7 @@ def load_library() -> C.CDLL:
         "tpimd5_s3_etag_file": (i32, [vp, C.c_char_p, u64, u64, vp, vp, C.POINTER(u32)]),
         "tpimd5_s3_plan_parts": (u32, [u64, u64, u64, u32, C.POINTER(i32), C.POINTER(u64)]),
         "tpimd5_units_extent": (C.c_int, [vp, vp, vp, C.c_size_t, C.POINTER(u64)]),
+        "tpimd5_ingest_probe": (i32, [vp, vp, vp, vp, sz, C.POINTER(sz)]),
         "tpimd5_s3_upload_plan": (i32, [vp, C.c_char_p, u64, u64, u64, u32, u32, vp, vp, vp]),
         "tpimd5_stream_open": (i32, [vp, C.POINTER(vp)]),
         "tpimd5_stream_write": (i32, [vp, vp, sz]),
@@ -294,6 +295,18 @@ class Context:
             e.failed_index = None if failed.value == C.c_size_t(-1).value else int(failed.value)
             raise e
         return out
+
+    def ingest_probe(self, paths, sizes, file_offsets=None) -> None:
+        """Reads the listed file ranges into the staging buffers the way hash_files does and stops there (no copy
+        to the device, no hashing): the host-ingest ceiling of the file entry points."""
+        pl = paths if isinstance(paths, PathList) else PathList(paths)
+        sz = np.ascontiguousarray(sizes, dtype=np.uint64)
+        fo = None if file_offsets is None else np.ascontiguousarray(file_offsets, dtype=np.uint64)
+        if sz.size != pl.n or (fo is not None and fo.size != pl.n):
+            raise ValueError("paths, sizes and file_offsets must have the same length")
+        failed = C.c_size_t()
+        _check(self._L.tpimd5_ingest_probe(self._h, C.cast(pl.array, C.c_void_p), None if fo is None else fo.ctypes.data,
+                                           sz.ctypes.data, pl.n, C.byref(failed)))
 
     def s3_etag_buffer(self, data, part_size: int):
         """-> (etag_md5 bytes, nparts, part_digests uint8[nparts, 16])."""

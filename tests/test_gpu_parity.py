@@ -178,6 +178,29 @@ def test_long_units_are_hashed_in_slices_side_by_side(tmp_path, staging):
             assert e.value.code == -4 and e.value.failed_index == 12
 
 
+def test_ingest_probe_reads_what_hash_files_reads(ctx, tmp_path):
+    """tpimd5_ingest_probe (the host-ingest ceiling bench.py quotes): same planning and reads as hash_files, no
+    digests; a file that is missing or shorter than listed is the same error, with its index."""
+    sizes = [0, 5, 70000, (3 << 20) + 1]
+    paths = []
+    for i, n in enumerate(sizes):
+        p = tmp_path / f"p{i}.bin"
+        p.write_bytes(oracle.synth_bytes(41, i, n).tobytes())
+        paths.append(str(p))
+    before = ctx.launch_count()
+    ctx.ingest_probe(paths, sizes)
+    ctx.ingest_probe([paths[3]] * 3, [1 << 20, 1 << 20, (1 << 20) + 1], file_offsets=[0, 1 << 20, 2 << 20])
+    assert ctx.launch_count() == before                       # nothing was hashed
+    with pytest.raises(tpi.TpiMd5Error) as e:
+        ctx.ingest_probe(paths, [0, 5, 70001, sizes[3]])
+    assert e.value.code == -4
+    with pytest.raises(tpi.TpiMd5Error):
+        ctx.ingest_probe(paths + [str(tmp_path / "missing")], sizes + [1])
+    got = ctx.hash_files(paths, sizes)                        # and the context still hashes afterwards
+    for i, n in enumerate(sizes):
+        assert got[i].tobytes() == oracle.md5(oracle.synth_bytes(41, i, n))
+
+
 def test_stream_is_a_go_hash(ctx):
     data = oracle.synth_bytes(26, 0, (9 << 20) + 13).tobytes()
     s, o = ctx.stream(), oracle.MD5Stream()
