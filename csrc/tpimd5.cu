@@ -1424,7 +1424,9 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
     if (job.paths) {
         by_size.resize(units_in.size());
         for (size_t i = 0; i < by_size.size(); ++i) by_size[i] = units_in[i];
-        std::stable_sort(by_size.begin(), by_size.end(), [&](uint32_t a, uint32_t b) { return job.len[a] > job.len[b]; });
+        auto longer = [&](uint32_t a, uint32_t b) { return job.len[a] > job.len[b]; };
+        if (!std::is_sorted(by_size.begin(), by_size.end(), longer))          // (a listing of equal files: nothing to sort)
+            std::stable_sort(by_size.begin(), by_size.end(), longer);
     }
     const UnitList units = job.paths ? UnitList{by_size.data(), 0, by_size.size()} : units_in;
     USE_DEVICE(s.dev);
@@ -1812,7 +1814,11 @@ static int run_device_impl(tpimd5_ctx *ctx, Slot &s, Job &job, const UnitList &u
             // (Only for a call's first batches, and only when they hold units of a MiB or more: units come longest first, so that is where the chains that bound the
             // call start; once the pipeline streams, the extra copies just take memory bandwidth from the readers:
             // an 8 GiB file went 250 -> 262 ms with slices on every batch, C1 72 -> 70 ms either way.)
-            ctx->pool->parallel_for(tasks.size(), 1, fill_mark, (used >= (64u << 20) && batch < 6 && longest >= (1u << 20)) ? &tick : nullptr);
+            // When the reads are the slow side anyway (small files: open/close bound, ~17 GB/s against 55 for the copy)
+            // every batch is copied as it fills: the copy of a whole buffer no longer trails its last read.
+            const bool slow_reads = from_files && ctx->feed_files.load() < 25e9;
+            ctx->pool->parallel_for(tasks.size(), 1, fill_mark,
+                                    (used >= (64u << 20) && ((batch < 6 && longest >= (1u << 20)) || slow_reads)) ? &tick : nullptr);
             const double fill_s = trace_now() - tr_f0;
             tr_fill += fill_s;
             if (used >= (16u << 20) && fill_s > 0) {
