@@ -77,7 +77,11 @@ TPIMD5_API const char *tpimd5_version(void);
  * goroutines call one file at a time under operations.CheckHashes (reached from
  * storage.go:158).  Unit i is bytes [offsets[i], offsets[i]+lengths[i]) of `base`
  * (hash_buffers) or the file paths[i] (hash_files; sizes may be NULL = fstat).  Units are
- * spread byte-balanced over the context's devices.  digests_out: 16*n bytes. */
+ * spread byte-balanced over the context's devices.  digests_out: 16*n bytes.
+ * Read pattern of hash_files: files are read longest first, with open/pread/close by the library's reader
+ * threads; files above half a staging buffer -- and, when many equal long files or parts follow one another,
+ * files from 4 MiB -- are read in slices (>= 1/384 of a staging buffer each), up to 384 files side by side, not
+ * front to back one after the other.  A file is open only while one of its ranges is being read. */
 TPIMD5_API int tpimd5_hash_buffers(tpimd5_ctx *ctx, const uint8_t *base, const uint64_t *offsets, const uint64_t *lengths,
                         size_t n, uint8_t *digests_out);
 TPIMD5_API int tpimd5_hash_files(tpimd5_ctx *ctx, const char *const *paths, const uint64_t *sizes, size_t n,
