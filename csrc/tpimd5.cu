@@ -2073,14 +2073,30 @@ extern "C" int tpimd5_hash_files(tpimd5_ctx *ctx, const char *const *paths, cons
     if (!paths || !digests_out) return fail(TPIMD5_EINVAL, "hash_files: null pointer");
     std::vector<uint64_t> st_sizes;
     if (!sizes) {
+        // (a listing of 200,000 files is 0.1 s of stat calls on one thread: the pool makes them, 4 Ki files per item;
+        // the error reported is the first one in listing order)
         st_sizes.resize(n);
-        for (size_t i = 0; i < n; ++i) {
-            struct stat sb;
-            if (stat(paths[i], &sb) != 0) {
-                if (failed_index_out) *failed_index_out = i;
-                return fail(TPIMD5_EIO, "unit %zu (%s): %s", i, paths[i], strerror(errno));
+        constexpr size_t CHUNK = 4096;
+        std::atomic<size_t> first_bad{(size_t)-1};
+        std::vector<int> bad_errno((n + CHUNK - 1) / CHUNK, 0);
+        std::function<void(size_t)> stat_chunk = [&](size_t c) {
+            const size_t hi = std::min(n, (c + 1) * CHUNK);
+            for (size_t i = c * CHUNK; i < hi; ++i) {
+                struct stat sb;
+                if (stat(paths[i], &sb) != 0) {
+                    bad_errno[c] = errno;
+                    size_t cur = first_bad.load();
+                    while (i < cur && !first_bad.compare_exchange_weak(cur, i)) {}
+                    return;
+                }
+                st_sizes[i] = (uint64_t)sb.st_size;
             }
-            st_sizes[i] = (uint64_t)sb.st_size;
+        };
+        ctx->pool->parallel_for((n + CHUNK - 1) / CHUNK, 1, stat_chunk);
+        if (first_bad.load() != (size_t)-1) {
+            const size_t i = first_bad.load();
+            if (failed_index_out) *failed_index_out = i;
+            return fail(TPIMD5_EIO, "unit %zu (%s): %s", i, paths[i], strerror(bad_errno[i / CHUNK]));
         }
         sizes = st_sizes.data();
     }
